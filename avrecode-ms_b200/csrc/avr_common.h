@@ -1,0 +1,93 @@
+// Shared host/device definitions for the avrecode entropy hot path (B200 build).
+//
+// Record format: what the host-side parse (libavcodec-hooks recorder, or the native
+// slice_data parser in h264_syntax.h) hands to the device compress path.  It restates, as
+// flat arrays, the event stream the reference's hooks deliver one callback at a time
+// (reference ffmpeg/libavcodec/coding_hooks.h:27-55; recode.cpp:150-215).
+#pragma once
+#include <stdint.h>
+#include <stddef.h>
+
+#if defined(__CUDACC__)
+#define AVR_HD __host__ __device__ __forceinline__
+#define AVR_HDN __host__ __device__
+#else
+#define AVR_HD inline
+#define AVR_HDN
+#endif
+
+// ---- bin record (u16) --------------------------------------------------------------------
+// bit 0      : symbol
+// bits 1..11 : context code: 0..1023 = ctxIdx (offset of the state byte in
+//              H264SliceContext::cabac_state, reference ffmpeg/libavcodec/h264.h:511),
+//              1024 = bypass, 1025 = terminate  (reference recode.cpp:1056,1190,1197)
+// bits 12..13: kind: 0 = coded immediately (default key), 1 = significance-map MAP bin,
+//              2 = significance-map EOB bin (queued on compress; never range-coded)
+#define AVR_CTX_BYPASS 1024
+#define AVR_CTX_TERMINATE 1025
+#define AVR_NUM_CTX_KEYS 1026
+#define AVR_KIND_DEFAULT 0
+#define AVR_KIND_SIG_MAP 1
+#define AVR_KIND_SIG_EOB 2
+#define AVR_BIN(sym, ctx, kind) ((uint16_t)(((sym) & 1) | ((ctx) << 1) | ((kind) << 12)))
+#define AVR_BIN_SYM(b) ((b) & 1)
+#define AVR_BIN_CTX(b) (((b) >> 1) & 0x7FF)
+#define AVR_BIN_KIND(b) (((b) >> 12) & 3)
+
+// ---- residual block record (16 B): one per begin_sub_mb..end_sub_mb (h264_cabac.c:1652-1779)
+typedef struct AvrBlock {
+  uint32_t bin_start;   // index (file-global) of the block's first significance-map bin
+  uint32_t mb_addr;     // mb_x + mb_y * mb_width   (mb_xy hook, h264_slice.c:2380)
+  uint32_t frame;       // index into AvrFrame[] (one per frame-buffer flip, recode.cpp:831-850)
+  uint8_t n;            // scan8 block index 0..50 (h264.h:1001-1002)
+  uint8_t cat_flags;    // bits0-3 ctxBlockCat 0..13, bit4 is_dc, bit5 chroma422
+  uint8_t max_coeff;    // 4, 8, 15, 16 or 64
+  uint8_t nbins;        // number of significance-map bins (MAP + EOB) recorded, <= 126
+} AvrBlock;
+
+// ---- coded slice record: one per init_decoder whose block was found (recode.cpp:1143-1164)
+typedef struct AvrSlice {
+  uint32_t bin_start, bin_end;      // [start,end) in the file's bin array (terminate(1) included)
+  uint32_t block_start, block_end;  // [start,end) in the file's AvrBlock array
+} AvrSlice;
+
+// ---- frame record: one per update_frame_spec() that flipped (recode.cpp:831-850)
+typedef struct AvrFrame {
+  uint16_t mb_w, mb_h;
+  uint32_t prev_valid;  // 1 if frames[!cur] holds the previous flip with the same dims
+} AvrFrame;
+
+// ---- estimator key space (dense re-indexing of reference model_key, recode.cpp:325,683-822,891)
+// default keys   : [0, 1026)                    key = ctx code
+// sig-map keys   : AVR_KEY_SIG_BASE + ((cat*64 + nnz)*64 + obs)*16 + zz_off
+//                  cat<14, nnz<64 (stored count, recode.cpp:928-931), obs<64, zz_off<16
+// nnz-bit keys   : AVR_KEY_NZ_BASE + (((i*64 + so_far)*18 + nb18)*64 + third)
+//                  i<6, so_far<64, nb18 = prev + 2*left + 6*above (each of left/above in 0..2),
+//                  third = is_8x8 + 2*is_dc + c422 + 4*cat  (<64)
+#define AVR_KEY_SIG_BASE 1026u
+#define AVR_KEY_SIG_COUNT (14u * 64u * 64u * 16u)
+#define AVR_KEY_NZ_BASE (AVR_KEY_SIG_BASE + AVR_KEY_SIG_COUNT)
+#define AVR_KEY_NZ_COUNT (6u * 64u * 18u * 64u)
+#define AVR_KEY_COUNT (AVR_KEY_NZ_BASE + AVR_KEY_NZ_COUNT)
+#define AVR_KEY_BITS 21
+
+static AVR_HD uint32_t avr_key_sig(int cat, int nnz_stored, int obs, int zz_off) {
+  return AVR_KEY_SIG_BASE + ((((uint32_t)cat * 64u + (uint32_t)nnz_stored) * 64u + (uint32_t)obs) * 16u + (uint32_t)zz_off);
+}
+static AVR_HD uint32_t avr_key_nz(int i, int so_far, int prev, int left, int above, int third) {
+  return AVR_KEY_NZ_BASE + (((((uint32_t)i * 64u + (uint32_t)so_far) * 18u + (uint32_t)(prev + 2 * left + 6 * above)) * 64u) + (uint32_t)third);
+}
+// halving threshold by key class (reference recode.cpp:1048-1049): sig-map keys 0x50, all others 0x60
+static AVR_HD int avr_key_is_sig(uint32_t key) { return key >= AVR_KEY_SIG_BASE && key < AVR_KEY_NZ_BASE; }
+
+// nnz side-channel width (reference recode.cpp:865)
+static AVR_HD int avr_nz_bits(int max_coeff) { return max_coeff > 16 ? 6 : max_coeff > 4 ? 4 : 2; }
+
+// error codes (C-ABI, include/avrecode_b200.h)
+#define AVR_OK 0
+#define AVR_E_ARG -1
+#define AVR_E_CUDA -2
+#define AVR_E_OVERFLOW -3
+#define AVR_E_UNSUPPORTED -4
+#define AVR_E_CORRUPT -5
+#define AVR_E_NOMEM -6

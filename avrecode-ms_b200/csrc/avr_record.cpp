@@ -1,0 +1,91 @@
+// Native compress-side front end: Annex-B H.264 -> record arrays, no libavcodec.
+// Does what libavcodec-hooks + compressor::cabac_decoder do together in the reference
+// (recode.cpp:1141-1199: a private standard CABAC decode of the ORIGINAL bytes whose bins are
+// handed to the model), plus compressor::find_next_coded_block_and_emit_literal's decision
+// (recode.cpp:1282-1304) of which slices are recoded and which stay literal.
+#include "avr_record.h"
+#include <string.h>
+#include "cabac_std.h"
+#include "h264_headers.h"
+
+namespace avr {
+namespace {
+
+struct RecordIO {
+  CabacDecoder dec;
+  uint8_t st[1024];
+  Recorder& rec;
+  explicit RecordIO(Recorder& r) : rec(r) {}
+  int get(int ctx) { int s = dec.decode(&st[ctx]); rec.bin(ctx, s); return s; }
+  int bypass(int) { int s = dec.bypass(); rec.bin(AVR_CTX_BYPASS, s); return s; }
+  int terminate(int) { int s = dec.terminate(); rec.bin(AVR_CTX_TERMINATE, s); return s; }
+  void mb_begin(int x, int y) { rec.mb_xy(x, y); }
+  void sub_mb_begin(int cat, int n, int mc, int dc, int c422) { rec.begin_sub_mb(cat, n, mc, dc, c422); }
+  void sub_mb_end() {}
+  void sigmap_begin() { rec.begin_sigmap(); }
+  void sigmap_end() { rec.end_sigmap(); }
+  void hint(int, int) {}
+};
+
+}  // namespace
+
+int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
+  Recorder rec(out, trace);
+  std::vector<Sps> sps(32);
+  std::vector<Pps> pps(256);
+  std::vector<uint8_t> rbsp;
+  std::vector<uint32_t> map;
+  std::vector<MbInfo> row;
+  uint32_t uid = 0;
+  size_t prev_coded_end = 0;
+  size_t pos = 0;
+  NalSpan nal;
+  while (next_nal(data, n, pos, &nal)) {
+    pos = nal.end;
+    const uint8_t hdr = data[nal.start];
+    const int type = hdr & 31, ref_idc = hdr >> 5;
+    if (type != 1 && type != 5 && type != 7 && type != 8) continue;
+    unescape_nal(data + nal.start + 1, nal.end - nal.start - 1, &rbsp, &map);
+    size_t len = rbsp.size();
+    while (len > 0 && rbsp[len - 1] == 0) len--;   // decode_nal_units trailing-zero strip
+    if (len == 0) continue;
+    if (type == 7) { Sps s; int id; if (parse_sps(rbsp.data(), len, &s, &id)) sps[id] = s; continue; }
+    if (type == 8) { Pps p; int id; if (parse_pps(rbsp.data(), len, sps.data(), &p, &id)) pps[id] = p; continue; }
+    // slice
+    int r = 0; { uint8_t v = rbsp[len - 1]; while (!(v & 1)) { v >>= 1; r++; } r++; }  // decode_rbsp_trailing
+    const size_t bit_length = 8 * len - (size_t)r;
+    SliceHeaderInfo sh;
+    if (!parse_slice_header(rbsp.data(), bit_length, type, ref_idc, sps.data(), pps.data(), &sh)) continue;
+    if (!sh.cabac) { out->error = AVR_E_UNSUPPORTED; return out->error; }   // CAVLC: nothing to recode
+    if (!sh.supported) { out->error = AVR_E_UNSUPPORTED; return out->error; }
+    if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);  // h264_frame_start
+    const size_t start = (sh.header_bits + 7) / 8;
+    if (bit_length <= 8 * start) continue;
+    const size_t size = (bit_length - 8 * start + 7) / 8;
+    const uint8_t* payload = rbsp.data() + start;
+    const size_t raw_off = nal.start + 1 + map[start];
+    // recode.cpp:1283-1286: memmem of the unescaped payload in the not-yet-emitted original bytes
+    bool found = false;
+    size_t found_at = 0;
+    if (size >= 8 && raw_off >= prev_coded_end) {
+      size_t hay_end = raw_off + size <= n ? raw_off + size : n;
+      const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, payload, size);
+      if (m) { found = true; found_at = (size_t)((const uint8_t*)m - data); }
+    }
+    rec.slice_begin(found, found ? found_at : raw_off, (uint32_t)size, sh.sp);
+    if (found) {
+      prev_coded_end = found_at + size;
+      if ((int)row.size() < sh.sp.mb_w) { row.resize((size_t)sh.sp.mb_w); for (auto& m : row) m.uid = 0; }
+      RecordIO io(rec);
+      io.dec.init(payload, size);
+      cabac_init_states(io.st, sh.sp.slice_type == SLICE_I, sh.sp.cabac_init_idc, sh.sp.slice_qp);
+      SliceParser<RecordIO> parser(io, sh.sp, row.data(), ++uid);
+      int rc = parser.run();
+      rec.slice_end();
+      if (rc < 0) { out->error = rc == SYN_E_PCM ? AVR_E_UNSUPPORTED : AVR_E_CORRUPT; return out->error; }
+    }
+  }
+  return AVR_OK;
+}
+
+}  // namespace avr

@@ -1,0 +1,133 @@
+// Host recorder: turns the hook event stream of one file into the flat record arrays of
+// avr_common.h.  Its methods are 1:1 with the reference's AVCodecHooks callbacks
+// (ffmpeg/libavcodec/coding_hooks.h:27-55, trampolines at recode.cpp:150-215), so it can be
+// driven either by libavcodec-hooks itself or by the native parser
+// (avr_record.cpp).
+#pragma once
+#include <stdint.h>
+#include <stdio.h>
+#include <vector>
+#include "avr_common.h"
+#include "h264_syntax.h"
+
+namespace avr {
+
+// One init_decoder call, in decode order (reference recode.cpp:1143-1164, 1282-1304).
+struct SliceSpan {
+  uint64_t payload_off;   // file offset of the first CABAC byte
+  uint32_t size;          // CABAC payload size libavcodec reports (h264_slice.c:2361-2364)
+  int32_t slice_index;    // index into FileRecord::slices, or -1 if skip_coded
+  uint32_t frame;         // frame-flip index current at this slice
+  SliceParams sp;         // header fields the device-side parser needs on decompress
+};
+
+struct FileRecord {
+  std::vector<uint16_t> bins;
+  std::vector<AvrBlock> blocks;
+  std::vector<AvrSlice> slices;
+  std::vector<AvrFrame> frames;
+  std::vector<SliceSpan> spans;
+  uint64_t source_bins = 0;   // get/get_bypass/get_terminate calls on coded slices (SURVEY 8d "bin")
+  int out_of_domain = 0;      // bit0: consecutive pictures share frame_num (recode.cpp:831-834 skips bzero)
+  int error = 0;              // AVR_E_* from the parse
+};
+
+class Recorder {
+ public:
+  explicit Recorder(FileRecord* r, FILE* trace = nullptr) : r_(r), trace_(trace) {}
+
+  // ModelHooks::frame_spec -> h264_model::update_frame_spec (recode.cpp:831-850)
+  void frame_spec(int frame_num, int mb_w, int mb_h) {
+    if (have_ && mb_w == w_ && mb_h == h_ && frame_num == frame_num_) {
+      r_->out_of_domain |= 1;
+      return;
+    }
+    AvrFrame f;
+    f.mb_w = (uint16_t)mb_w; f.mb_h = (uint16_t)mb_h;
+    f.prev_valid = (have_ && mb_w == w_ && mb_h == h_) ? 1u : 0u;
+    r_->frames.push_back(f);
+    have_ = true; w_ = mb_w; h_ = mb_h; frame_num_ = frame_num;
+  }
+  uint32_t cur_frame() const { return r_->frames.empty() ? 0u : (uint32_t)r_->frames.size() - 1; }
+
+  // CABACCodingHooks::init_decoder. coded=false is the skip_coded path (hooks disabled).
+  void slice_begin(bool coded, uint64_t payload_off, uint32_t size, const SliceParams& sp) {
+    SliceSpan s;
+    s.payload_off = payload_off; s.size = size; s.sp = sp; s.frame = cur_frame();
+    s.slice_index = coded ? (int32_t)r_->slices.size() : -1;
+    r_->spans.push_back(s);
+    coded_ = coded;
+    if (trace_) {
+      fprintf(trace_, "F %d %d %d\n", (int)(r_->frames.size() & 1), w_, h_);
+      fprintf(trace_, "S %u\n", size);
+    }
+    if (coded) {
+      AvrSlice sl;
+      sl.bin_start = sl.bin_end = (uint32_t)r_->bins.size();
+      sl.block_start = sl.block_end = (uint32_t)r_->blocks.size();
+      r_->slices.push_back(sl);
+    }
+    in_sigmap_ = false;
+  }
+  void slice_end() {
+    if (!coded_) return;
+    r_->slices.back().bin_end = (uint32_t)r_->bins.size();
+    r_->slices.back().block_end = (uint32_t)r_->blocks.size();
+  }
+  void mb_xy(int x, int y) {
+    mb_addr_ = (uint32_t)(x + y * w_);
+    if (trace_) fprintf(trace_, "M %d %d\n", x, y);
+  }
+  void begin_sub_mb(int cat, int n, int max_coeff, int is_dc, int c422) {
+    cat_ = cat; n_ = n; max_coeff_ = max_coeff; is_dc_ = is_dc; c422_ = c422;
+  }
+  void begin_sigmap() {
+    if (trace_) fprintf(trace_, "B %d %d %d %d %d\n[\n", cat_, n_, max_coeff_, is_dc_, c422_);
+    if (!coded_) return;
+    AvrBlock b;
+    b.bin_start = (uint32_t)r_->bins.size();
+    b.mb_addr = mb_addr_;
+    b.frame = cur_frame();
+    b.n = (uint8_t)n_;
+    b.cat_flags = (uint8_t)(cat_ | (is_dc_ << 4) | (c422_ << 5));
+    b.max_coeff = (uint8_t)max_coeff_;
+    b.nbins = 0;
+    r_->blocks.push_back(b);
+    in_sigmap_ = true; expect_eob_ = false;
+  }
+  void end_sigmap() {
+    if (trace_) fprintf(trace_, "]\n");
+    in_sigmap_ = false;
+  }
+  // get / get_bypass / get_terminate
+  void bin(int ctx, int sym) {
+    if (trace_) {
+      if (ctx == AVR_CTX_BYPASS) fprintf(trace_, "b %d\n", sym);
+      else if (ctx == AVR_CTX_TERMINATE) fprintf(trace_, "t %d\n", sym);
+      else fprintf(trace_, "c %d %d\n", ctx, sym);
+    }
+    if (!coded_) return;
+    int kind = AVR_KIND_DEFAULT;
+    if (in_sigmap_) {
+      kind = expect_eob_ ? AVR_KIND_SIG_EOB : AVR_KIND_SIG_MAP;
+      expect_eob_ = !expect_eob_ && sym;   // MAP bin = 1 -> next is its EOB bin (recode.cpp:998-1000)
+      r_->blocks.back().nbins++;
+    }
+    r_->bins.push_back(AVR_BIN(sym, ctx, kind));
+    r_->source_bins++;
+  }
+
+ private:
+  FileRecord* r_;
+  FILE* trace_;
+  bool have_ = false; int w_ = 0, h_ = 0, frame_num_ = 0;
+  bool coded_ = false, in_sigmap_ = false, expect_eob_ = false;
+  uint32_t mb_addr_ = 0;
+  int cat_ = 0, n_ = 0, max_coeff_ = 0, is_dc_ = 0, c422_ = 0;
+};
+
+// Native front end: parse an Annex-B H.264 byte stream without libavcodec.
+// Returns AVR_OK, AVR_E_UNSUPPORTED (stream uses syntax outside h264_syntax.h) or AVR_E_CORRUPT.
+int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace = nullptr);
+
+}  // namespace avr

@@ -41,6 +41,6 @@ $CXX $FLAGS $INC -c "$REF/test.cpp" -o "$SCRATCH/test.o"
 $CXX "$SCRATCH/recode.o" "$SCRATCH/test.o" -o "$OUT/recode" $LIBS
 $CXX -std=c++17 -O2 -w $INC "$REF/test/arithmetic_code.cpp" -o "$OUT/arith_test" $LIBS
 if [ -f "$HERE/ref_harness.cpp" ]; then
-  $CXX $FLAGS $INC -DAVR_REF_DIR="\"$REF\"" "$HERE/ref_harness.cpp" -o "$OUT/ref_harness" $LIBS
+  $CXX $FLAGS $INC -DAVR_REF_DIR="\"$REF\"" "$HERE/ref_harness.cpp" "$SCRATCH/test.o" -o "$OUT/ref_harness" $LIBS
 fi
 echo "built: $(ls "$OUT")"

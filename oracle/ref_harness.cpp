@@ -1,0 +1,100 @@
+// TEST INFRASTRUCTURE -- drives the UNMODIFIED reference classes; never linked into the product.
+//
+// Includes the reference's recode.cpp as-is (main renamed) and adds a third `Driver` for its
+// av_decoder<> template (reference recode.cpp:80-237) next to `compressor`/`decompressor`:
+//   ref_harness trace <file.h264>      : dump every hook event libavcodec-hooks delivers
+//                                        (the ground truth for avrecode-ms_b200/csrc/h264_syntax.h)
+// Output, one event per line:
+//   F cur_frame w h            (after a frame flip is observed)
+//   S size                     (init_decoder: new slice, `size` bytes of CABAC payload)
+//   M x y                      (macroblock change)
+//   B cat n max_coeff is_dc c422   (begin_sub_mb observed)
+//   [ / ]                      (begin/end_coding_type SIGNIFICANCE_MAP)
+//   c <ctxIdx> <sym> | b <sym> | t <sym>
+#define main recode_main
+#include "recode.cpp"
+#undef main
+
+class tracer {
+ public:
+  tracer(const std::string& fn) : input_filename(fn) {
+    if (av_file_map(fn.c_str(), &bytes, &size, 0, NULL) < 0) throw std::invalid_argument("open " + fn);
+  }
+  void run() {
+    av_decoder<tracer> d(this, input_filename);
+    d.decode_video();
+  }
+  int read_packet(uint8_t* out, int n) {
+    n = std::min(n, int(size - off));
+    memcpy(out, bytes + off, n);
+    off += n;
+    return n;
+  }
+  h264_model* get_model() { return &model; }
+
+  class cabac_decoder {
+   public:
+    cabac_decoder(tracer* t, CABACContext* ctx_in, const uint8_t* buf, int size) : t(t) {
+      ctx = *ctx_in;
+      ctx.coding_hooks = nullptr;
+      ctx.coding_hooks_opaque = nullptr;
+      ::ff_reset_cabac_decoder(&ctx, buf, size);
+      base = (const uint8_t*)ctx_in + sizeof(CABACContext);  // H264SliceContext::cabac_state follows ::cabac (h264.h:510-511)
+      h264_model* m = &t->model;
+      printf("F %d %u %u\n", m->cur_frame, m->frames[m->cur_frame].width(), m->frames[m->cur_frame].height());
+      printf("S %d\n", size);
+      last_x = last_y = -1;
+    }
+    void sync() {
+      h264_model* m = &t->model;
+      if (m->mb_coord.mb_x != last_x || m->mb_coord.mb_y != last_y) {
+        last_x = m->mb_coord.mb_x; last_y = m->mb_coord.mb_y;
+        printf("M %d %d\n", last_x, last_y);
+      }
+    }
+    int get(uint8_t* state) {
+      sync();
+      int s = ::ff_get_cabac(&ctx, state);
+      printf("c %d %d\n", int(state - base), s);
+      return s;
+    }
+    int get_bypass() { sync(); int s = ::ff_get_cabac_bypass(&ctx); printf("b %d\n", s); return s; }
+    int get_terminate() { sync(); int s = ::ff_get_cabac_terminate(&ctx) != 0; printf("t %d\n", s); return s; }
+    void begin_coding_type(CodingType ct, int, int, int) {
+      sync();
+      h264_model* m = &t->model;
+      printf("B %d %d %d %d %d\n", m->sub_mb_cat, m->mb_coord.scan8_index, m->sub_mb_size, m->sub_mb_is_dc, m->sub_mb_chroma422);
+      printf("[\n");
+    }
+    void end_coding_type(CodingType ct) { printf("]\n"); }
+   private:
+    tracer* t;
+    CABACContext ctx;
+    const uint8_t* base;
+    int last_x, last_y;
+  };
+
+ private:
+  std::string input_filename;
+  uint8_t* bytes = nullptr;
+  size_t size = 0;
+  int off = 0;
+  h264_model model;
+};
+
+int main(int argc, char** argv) {
+  av_register_all();
+  av_log_set_level(AV_LOG_ERROR);
+  if (argc >= 3 && std::string(argv[1]) == "trace") {
+    try {
+      tracer t(argv[2]);
+      t.run();
+    } catch (const std::exception& e) {
+      fprintf(stderr, "Exception: %s\n", e.what());
+      return 1;
+    }
+    return 0;
+  }
+  fprintf(stderr, "usage: %s trace <file>\n", argv[0]);
+  return 1;
+}
