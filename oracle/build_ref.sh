@@ -17,6 +17,9 @@ REF="${AVR_REFERENCE:-/root/reference}"
 OUT="$HERE/_ref"
 SCRATCH="${AVR_REF_SCRATCH:-/tmp/avr_ref}"
 JOBS="${JOBS:-$(nproc)}"
+mkdir -p "$OUT"
+# the CPU restatement (needs no reference sources)
+${CXX:-g++} -std=c++17 -O2 -o "$OUT/avr_oracle" "$HERE/avr_oracle.cpp"
 [ -d "$REF/ffmpeg/libavcodec" ] || { echo "reference not present at $REF; keeping prebuilt $OUT" >&2; exit 0; }
 mkdir -p "$OUT" "$SCRATCH/ffbuild"
 

@@ -6,7 +6,10 @@
 //                                        (the ground truth for avrecode-ms_b200/csrc/h264_syntax.h)
 // Output, one event per line:
 //   F cur_frame w h            (after a frame flip is observed)
-//   S size                     (init_decoder: new slice, `size` bytes of CABAC payload)
+//   S size off                 (init_decoder: new slice, `size` bytes of CABAC payload; off = file
+//                               offset found by the compressor's memmem rule, recode.cpp:1282-1304,
+//                               or -1 when the slice stays literal / skip_coded: its bins are not traced)
+//   I <2048 hex>               (the 1024 CABAC context states at the slice's first bin)
 //   M x y                      (macroblock change)
 //   B cat n max_coeff is_dc c422   (begin_sub_mb observed)
 //   [ / ]                      (begin/end_coding_type SIGNIFICANCE_MAP)
@@ -25,7 +28,7 @@ class tracer {
     d.decode_video();
   }
   int read_packet(uint8_t* out, int n) {
-    n = std::min(n, int(size - off));
+    n = std::min(n, int(size - (size_t)off));
     memcpy(out, bytes + off, n);
     off += n;
     return n;
@@ -35,18 +38,35 @@ class tracer {
   class cabac_decoder {
    public:
     cabac_decoder(tracer* t, CABACContext* ctx_in, const uint8_t* buf, int size) : t(t) {
+      h264_model* m = &t->model;
+      printf("F %d %u %u\n", m->cur_frame, m->frames[m->cur_frame].width(), m->frames[m->cur_frame].height());
+      // same decision as compressor::find_next_coded_block_and_emit_literal (recode.cpp:1282-1304)
+      uint8_t* found = static_cast<uint8_t*>(memmem(t->bytes + t->prev_end, t->off - t->prev_end, buf, size));
+      if (!(found && size >= SURROGATE_MARKER_BYTES)) {
+        printf("S %d -1\n", size);
+        ctx_in->coding_hooks = nullptr;
+        ctx_in->coding_hooks_opaque = nullptr;
+        ::ff_reset_cabac_decoder(ctx_in, buf, size);
+        skipped = true;
+        return;
+      }
+      printf("S %d %ld\n", size, (long)(found - t->bytes));
+      t->prev_end = (found - t->bytes) + size;
       ctx = *ctx_in;
       ctx.coding_hooks = nullptr;
       ctx.coding_hooks_opaque = nullptr;
       ::ff_reset_cabac_decoder(&ctx, buf, size);
       base = (const uint8_t*)ctx_in + sizeof(CABACContext);  // H264SliceContext::cabac_state follows ::cabac (h264.h:510-511)
-      h264_model* m = &t->model;
-      printf("F %d %u %u\n", m->cur_frame, m->frames[m->cur_frame].width(), m->frames[m->cur_frame].height());
-      printf("S %d\n", size);
       last_x = last_y = -1;
     }
     void sync() {
       h264_model* m = &t->model;
+      if (!states_dumped) {
+        states_dumped = true;
+        printf("I ");
+        for (int i = 0; i < 1024; i++) printf("%02x", base[i]);
+        printf("\n");
+      }
       if (m->mb_coord.mb_x != last_x || m->mb_coord.mb_y != last_y) {
         last_x = m->mb_coord.mb_x; last_y = m->mb_coord.mb_y;
         printf("M %d %d\n", last_x, last_y);
@@ -61,24 +81,26 @@ class tracer {
     int get_bypass() { sync(); int s = ::ff_get_cabac_bypass(&ctx); printf("b %d\n", s); return s; }
     int get_terminate() { sync(); int s = ::ff_get_cabac_terminate(&ctx) != 0; printf("t %d\n", s); return s; }
     void begin_coding_type(CodingType ct, int, int, int) {
+      if (skipped) return;
       sync();
       h264_model* m = &t->model;
       printf("B %d %d %d %d %d\n", m->sub_mb_cat, m->mb_coord.scan8_index, m->sub_mb_size, m->sub_mb_is_dc, m->sub_mb_chroma422);
       printf("[\n");
     }
-    void end_coding_type(CodingType ct) { printf("]\n"); }
+    void end_coding_type(CodingType ct) { if (!skipped) printf("]\n"); }
    private:
     tracer* t;
     CABACContext ctx;
     const uint8_t* base;
     int last_x, last_y;
+    bool skipped = false, states_dumped = false;
   };
 
  private:
   std::string input_filename;
   uint8_t* bytes = nullptr;
   size_t size = 0;
-  int off = 0;
+  long off = 0, prev_end = 0;
   h264_model model;
 };
 
