@@ -1,0 +1,148 @@
+// TEST SCAFFOLD (not part of the product library): compiles the kernel bodies of
+// avrecode-ms_b200/csrc for the HOST and runs them as an emulated grid, so the device logic can
+// be checked against the oracle in the GPU-less build container.  The product never links this.
+//   avr_emul chain <clip.h264>      single-thread compress body -> "P <hex>" per coded slice
+//   avr_emul pipeline <clip.h264>   slice-parallel compress pipeline (emulated) -> "P <hex>"
+//   avr_emul roundtrip <clip.h264>  compress, then decompress body; checks CABAC bytes == original
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../avrecode-ms_b200/csrc/avr_record.h"
+#include "../avrecode-ms_b200/csrc/avr_bodies.h"
+#include "../avrecode-ms_b200/csrc/avr_host_tables.h"
+#ifdef AVR_EMUL_PIPELINE
+#include "../avrecode-ms_b200/csrc/avr_pipeline.h"
+#endif
+
+static bool read_file(const char* fn, std::vector<uint8_t>* out) {
+  FILE* f = fopen(fn, "rb");
+  if (!f) return false;
+  fseek(f, 0, SEEK_END); long n = ftell(f); fseek(f, 0, SEEK_SET);
+  out->resize((size_t)n);
+  size_t got = fread(out->data(), 1, (size_t)n, f);
+  fclose(f);
+  return got == (size_t)n;
+}
+static void print_hex(const char* tag, const uint8_t* p, size_t n) {
+  fputs(tag, stdout);
+  for (size_t i = 0; i < n; i++) printf("%02x", p[i]);
+  fputc('\n', stdout);
+}
+
+struct Compressed {
+  std::vector<std::vector<uint8_t>> payloads;
+};
+
+static AvrFileDesc make_desc(const avr::FileRecord& rec) {
+  AvrFileDesc fd;
+  memset(&fd, 0, sizeof fd);
+  fd.nbins = (uint32_t)rec.bins.size();
+  fd.nblocks = (uint32_t)rec.blocks.size();
+  fd.nslices = (uint32_t)rec.slices.size();
+  fd.nframes = (uint32_t)rec.frames.size();
+  for (auto& f : rec.frames) if ((uint32_t)f.mb_w * f.mb_h > fd.max_mbs) fd.max_mbs = (uint32_t)f.mb_w * f.mb_h;
+  return fd;
+}
+
+static int compress_chain(const avr::FileRecord& rec, const AvrTables& tab, Compressed* out) {
+  AvrFileDesc fd = make_desc(rec);
+  std::vector<uint16_t> est(AVR_KEY_COUNT, AVR_EST_INIT);
+  std::vector<uint8_t> s0((size_t)fd.max_mbs * AVR_MB_STRIDE + 16), s1(s0.size());
+  std::vector<uint64_t> soff(fd.nslices); std::vector<uint32_t> scap(fd.nslices), olen(fd.nslices);
+  std::vector<int> status(fd.nslices);
+  uint64_t total = 0;
+  for (uint32_t s = 0; s < fd.nslices; s++) {
+    const AvrSlice& sl = rec.slices[s];
+    scap[s] = (sl.bin_end - sl.bin_start) + 6 * (sl.block_end - sl.block_start) + 16;
+    soff[s] = total; total += scap[s];
+  }
+  std::vector<uint8_t> scratch(total + 16);
+  avr_compress_chain_body(fd, rec.bins.data(), rec.blocks.data(), rec.slices.data(), rec.frames.data(), est.data(),
+                          s0.data(), s1.data(), &tab, scratch.data(), soff.data(), scap.data(), olen.data(), status.data());
+  for (uint32_t s = 0; s < fd.nslices; s++) {
+    if (status[s]) { fprintf(stderr, "slice %u status %d\n", s, status[s]); return status[s]; }
+    out->payloads.emplace_back(scratch.begin() + soff[s], scratch.begin() + soff[s] + olen[s]);
+  }
+  return 0;
+}
+
+static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRecord& rec, const AvrTables& tab, const Compressed& c) {
+  AvrFileDesc fd = make_desc(rec);
+  std::vector<AvrDecSlice> ds;
+  std::vector<uint8_t> pool;
+  uint64_t out_total = 0;
+  uint32_t last_frame = ~0u;
+  std::vector<const avr::SliceSpan*> spans;
+  for (auto& sp : rec.spans) {
+    if (sp.slice_index < 0) continue;
+    AvrDecSlice d;
+    memset(&d, 0, sizeof d);
+    d.payload_off = pool.size();
+    d.payload_len = (uint32_t)c.payloads[sp.slice_index].size();
+    pool.insert(pool.end(), c.payloads[sp.slice_index].begin(), c.payloads[sp.slice_index].end());
+    d.out_off = out_total; d.out_cap = sp.size + 64; out_total += d.out_cap;
+    if (sp.frame != last_frame) {
+      uint32_t k = last_frame == ~0u ? sp.frame + 1 : sp.frame - last_frame;
+      d.flip = (k == 1 && rec.frames[sp.frame].prev_valid) ? 1 : 2;
+      last_frame = sp.frame;
+    }
+    d.sp = sp.sp;
+    ds.push_back(d);
+    spans.push_back(&sp);
+  }
+  fd.nslices = (uint32_t)ds.size();
+  std::vector<uint16_t> est(AVR_KEY_COUNT, AVR_EST_INIT);
+  std::vector<uint8_t> s0((size_t)fd.max_mbs * AVR_MB_STRIDE + 16), s1(s0.size()), out(out_total + 16), st(1024);
+  std::vector<avr::MbInfo> row(4096);
+  std::vector<uint32_t> olen(ds.size()), obins(ds.size());
+  std::vector<int> status(ds.size());
+  pool.resize(pool.size() + 16);
+  avr_decompress_chain_body(fd, ds.data(), pool.data(), est.data(), s0.data(), s1.data(), row.data(), st.data(), &tab,
+                            out.data(), olen.data(), obins.data(), status.data());
+  int bad = 0;
+  uint64_t bins = 0;
+  for (size_t s = 0; s < ds.size(); s++) {
+    const avr::SliceSpan& sp = *spans[s];
+    const AvrSlice& sl = rec.slices[sp.slice_index];
+    bins += obins[s];
+    if (status[s]) { printf("slice %zu: status %d\n", s, status[s]); bad++; continue; }
+    if (obins[s] != sl.bin_end - sl.bin_start) { printf("slice %zu: bins %u != %u\n", s, obins[s], sl.bin_end - sl.bin_start); bad++; }
+    // reference fix-up (recode.cpp:1352-1362) then compare with the original bytes
+    std::vector<uint8_t> o(out.begin() + ds[s].out_off, out.begin() + ds[s].out_off + olen[s]);
+    uint8_t last = data[sp.payload_off + sp.size - 1];
+    if ((sp.size & 1) != (o.size() & 1)) o.push_back(last); else if (!o.empty()) o.back() = last;
+    if (o.size() != sp.size || memcmp(o.data(), data.data() + sp.payload_off, sp.size)) {
+      printf("slice %zu: CABAC bytes differ (len %zu vs %u)\n", s, o.size(), sp.size); bad++;
+    }
+  }
+  printf("%s slices=%zu bins=%llu\n", bad ? "FAIL" : "OK", ds.size(), (unsigned long long)bins);
+  return bad;
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) { fprintf(stderr, "usage: %s chain|pipeline|roundtrip <clip>\n", argv[0]); return 2; }
+  std::string cmd = argv[1];
+  std::vector<uint8_t> data;
+  if (!read_file(argv[2], &data)) { fprintf(stderr, "cannot read %s\n", argv[2]); return 2; }
+  avr::FileRecord rec;
+  int rc = avr::record_annexb(data.data(), data.size(), &rec);
+  if (rc) { fprintf(stderr, "record rc=%d\n", rc); return 1; }
+  AvrTables tab;
+  avr_fill_tables(&tab);
+  Compressed c;
+  if (cmd == "chain" || cmd == "roundtrip") {
+    if (compress_chain(rec, tab, &c)) return 1;
+  }
+#ifdef AVR_EMUL_PIPELINE
+  if (cmd == "pipeline") {
+    std::vector<std::vector<uint8_t>> p;
+    if (avr_pipeline_emulate(rec, tab, &p)) return 1;
+    c.payloads = p;
+  }
+#endif
+  if (cmd == "roundtrip") return decompress_check(data, rec, tab, c) ? 1 : 0;
+  for (auto& p : c.payloads) print_hex("P ", p.data(), p.size());
+  return 0;
+}
