@@ -23,8 +23,15 @@ struct AvrFileDesc {
   uint32_t slice_off, nslices;       // into slices[] (compress) / dec_slices[] (decompress)
   uint32_t frame_off, nframes;       // into frames[]
   uint32_t max_mbs;                  // largest picture of the file, in macroblocks
-  uint32_t mb_base;                  // first macroblock slot of this file in the chain stores / row pool
-  uint32_t pad;
+  uint32_t mb_base;                  // chain kernels: first macroblock slot of this file (2*max_mbs slots per file)
+  uint32_t pic_mb_base;              // pipeline: first macroblock slot of this file's per-picture stores
+};
+
+// Compress-side slice in batch coordinates (built by the host when a batch is staged).
+struct AvrBatchSlice {
+  uint32_t file;                     // index into fds[]
+  uint32_t bin_start, bin_end;       // file-local, as in AvrSlice
+  uint32_t block_start, block_end;   // batch-global block indices
 };
 
 // One coded slice on the decompress side (reference decompressor::cabac_decoder, recode.cpp:1418-1527).

@@ -55,6 +55,7 @@ typedef struct AvrSlice {
 typedef struct AvrFrame {
   uint16_t mb_w, mb_h;
   uint32_t prev_valid;  // 1 if frames[!cur] holds the previous flip with the same dims
+  uint32_t mb_base;     // macroblocks of the file's earlier pictures (slot of this picture's store)
 } AvrFrame;
 
 // ---- estimator key space (dense re-indexing of reference model_key, recode.cpp:325,683-822,891)

@@ -77,7 +77,9 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
       prev_coded_end = found_at + size;
       if ((int)row.size() < sh.sp.mb_w) { row.resize((size_t)sh.sp.mb_w); for (auto& m : row) m.uid = 0; }
       RecordIO io(rec);
-      io.dec.init(payload, size);
+      // libavcodec's CABAC reader may look one or two bytes past `size` (a lone 0x80 stop-bit byte
+      // is excluded from size but still in its buffer, cabac_functions.h refill): give ours the same view
+      io.dec.init(payload, rbsp.size() - start);
       cabac_init_states(io.st, sh.sp.slice_type == SLICE_I, sh.sp.cabac_init_idc, sh.sp.slice_qp);
       SliceParser<RecordIO> parser(io, sh.sp, row.data(), ++uid);
       int rc = parser.run();

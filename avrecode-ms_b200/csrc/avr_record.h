@@ -45,6 +45,7 @@ class Recorder {
     AvrFrame f;
     f.mb_w = (uint16_t)mb_w; f.mb_h = (uint16_t)mb_h;
     f.prev_valid = (have_ && mb_w == w_ && mb_h == h_) ? 1u : 0u;
+    f.mb_base = r_->frames.empty() ? 0u : r_->frames.back().mb_base + (uint32_t)r_->frames.back().mb_w * r_->frames.back().mb_h;
     r_->frames.push_back(f);
     have_ = true; w_ = mb_w; h_ = mb_h; frame_num_ = frame_num;
   }

@@ -12,9 +12,8 @@
 #include "../avrecode-ms_b200/csrc/avr_record.h"
 #include "../avrecode-ms_b200/csrc/avr_bodies.h"
 #include "../avrecode-ms_b200/csrc/avr_host_tables.h"
-#ifdef AVR_EMUL_PIPELINE
 #include "../avrecode-ms_b200/csrc/avr_pipeline.h"
-#endif
+#include <algorithm>
 
 static bool read_file(const char* fn, std::vector<uint8_t>* out) {
   FILE* f = fopen(fn, "rb");
@@ -64,6 +63,80 @@ static int compress_chain(const avr::FileRecord& rec, const AvrTables& tab, Comp
   for (uint32_t s = 0; s < fd.nslices; s++) {
     if (status[s]) { fprintf(stderr, "slice %u status %d\n", s, status[s]); return status[s]; }
     out->payloads.emplace_back(scratch.begin() + soff[s], scratch.begin() + soff[s] + olen[s]);
+  }
+  return 0;
+}
+
+// The slice-parallel compress pipeline with the launches of avr_kernels.cu replaced by loops and
+// the CUB plumbing (radix sort, scans) by std::stable_sort / serial scans.
+static int compress_pipeline(const std::vector<const avr::FileRecord*>& recs, const AvrTables& tab,
+                             std::vector<Compressed>* out) {
+  std::vector<AvrFileDesc> fds;
+  std::vector<uint16_t> bins; std::vector<AvrBlock> blocks; std::vector<AvrBatchSlice> bsl; std::vector<AvrFrame> frames;
+  uint32_t pic_mbs = 0;
+  for (size_t f = 0; f < recs.size(); f++) {
+    const avr::FileRecord& r = *recs[f];
+    AvrFileDesc fd = make_desc(r);
+    fd.bin_off = bins.size(); fd.block_off = (uint32_t)blocks.size(); fd.slice_off = (uint32_t)bsl.size();
+    fd.frame_off = (uint32_t)frames.size(); fd.pic_mb_base = pic_mbs;
+    for (auto& fr : r.frames) pic_mbs += (uint32_t)fr.mb_w * fr.mb_h;
+    for (auto& sl : r.slices) {
+      AvrBatchSlice b = {(uint32_t)f, sl.bin_start, sl.bin_end, sl.block_start + fd.block_off, sl.block_end + fd.block_off};
+      bsl.push_back(b);
+    }
+    bins.insert(bins.end(), r.bins.begin(), r.bins.end());
+    blocks.insert(blocks.end(), r.blocks.begin(), r.blocks.end());
+    frames.insert(frames.end(), r.frames.begin(), r.frames.end());
+    fds.push_back(fd);
+  }
+  AvrPipe a;
+  memset(&a, 0, sizeof a);
+  a.fds = fds.data(); a.bslices = bsl.data(); a.nslices = (uint32_t)bsl.size(); a.blocks = blocks.data();
+  a.nblocks = (uint32_t)blocks.size(); a.bins = bins.data(); a.frames = frames.data(); a.tab = &tab;
+  std::vector<uint8_t> store((size_t)pic_mbs * AVR_MB_STRIDE + 64, 0);
+  a.store = store.data();
+  const uint32_t nent = a.nblocks + a.nslices;
+  std::vector<uint32_t> seg(nent + 1, 0);
+  a.seg = seg.data();
+  for (uint32_t e = 0; e < nent; e++) avr_body_count(a, e);
+  uint32_t run = 0;
+  for (uint32_t e = 0; e <= nent; e++) { uint32_t c = seg[e]; seg[e] = run; run += c; }
+  a.nemit = run;
+  std::vector<uint32_t> keys(run), idx(run);
+  a.keys = keys.data();
+  for (uint32_t e = 0; e < nent; e++) avr_body_keys(a, e);
+  for (uint32_t i = 0; i < run; i++) idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](uint32_t x, uint32_t y) { return (keys[x] >> 1) < (keys[y] >> 1); });
+  std::vector<uint32_t> sorted(run), head(run), ones(run);
+  std::vector<AvrHalf> fn(run);
+  for (uint32_t i = 0; i < run; i++) sorted[i] = keys[idx[i]];
+  for (uint32_t i = 0; i < run; i++) {
+    bool kh = i == 0 || (sorted[i] >> 1) != (sorted[i - 1] >> 1);
+    head[i] = kh ? i : head[i - 1];
+    uint32_t r = i - head[i];
+    AvrPeriod p = avr_period_of((sorted[i] >> 1) & 0x1FFFFFu);
+    ones[i] = (avr_is_period_head(r, p) ? 0 : ones[i - 1]) + (sorted[i] & 1);
+    AvrHalf el = {0, 0};
+    if (avr_is_period_tail(r, p)) { el.a = ones[i]; el.k = 1; }
+    fn[i] = kh ? el : avr_half_compose(fn[i - 1], el);
+  }
+  std::vector<uint16_t> prob(run);
+  a.prob = prob.data();
+  for (uint32_t i = 0; i < run; i++) avr_body_estimate(i, sorted.data(), idx.data(), head.data(), ones.data(), fn.data(), prob.data());
+  std::vector<uint64_t> soff(a.nslices); std::vector<uint32_t> scap(a.nslices), olen(a.nslices);
+  std::vector<int> status(a.nslices);
+  uint64_t total = 0;
+  for (uint32_t s = 0; s < a.nslices; s++) {
+    scap[s] = (bsl[s].bin_end - bsl[s].bin_start) + 6 * (bsl[s].block_end - bsl[s].block_start) + 16;
+    soff[s] = total; total += scap[s];
+  }
+  std::vector<uint8_t> scratch(total + 16);
+  a.scratch = scratch.data(); a.scratch_off = soff.data(); a.scratch_cap = scap.data(); a.out_len = olen.data(); a.status = status.data();
+  for (uint32_t s = 0; s < a.nslices; s++) avr_body_code(a, s);
+  out->resize(recs.size());
+  for (uint32_t s = 0; s < a.nslices; s++) {
+    if (status[s]) { fprintf(stderr, "slice %u status %d\n", s, status[s]); return status[s]; }
+    (*out)[bsl[s].file].payloads.emplace_back(scratch.begin() + soff[s], scratch.begin() + soff[s] + olen[s]);
   }
   return 0;
 }
@@ -135,13 +208,19 @@ int main(int argc, char** argv) {
   if (cmd == "chain" || cmd == "roundtrip") {
     if (compress_chain(rec, tab, &c)) return 1;
   }
-#ifdef AVR_EMUL_PIPELINE
   if (cmd == "pipeline") {
-    std::vector<std::vector<uint8_t>> p;
-    if (avr_pipeline_emulate(rec, tab, &p)) return 1;
-    c.payloads = p;
+    // further clips on the command line join the batch; the first file's payloads are printed
+    std::vector<avr::FileRecord> extra((size_t)(argc > 3 ? argc - 3 : 0));
+    std::vector<const avr::FileRecord*> recs = {&rec};
+    for (int i = 3; i < argc; i++) {
+      std::vector<uint8_t> d2;
+      if (!read_file(argv[i], &d2) || avr::record_annexb(d2.data(), d2.size(), &extra[i - 3])) return 2;
+      recs.insert(recs.begin(), &extra[i - 3]);   // put them BEFORE so offsets are exercised
+    }
+    std::vector<Compressed> all;
+    if (compress_pipeline(recs, tab, &all)) return 1;
+    c = all.back();
   }
-#endif
   if (cmd == "roundtrip") return decompress_check(data, rec, tab, c) ? 1 : 0;
   for (auto& p : c.payloads) print_hex("P ", p.data(), p.size());
   return 0;
