@@ -1,0 +1,488 @@
+// C-ABI implementation (include/avrecode_b200.h): context, recorder bindings, staged
+// compress / decompress batches.  Owns device memory and the stream; all compute is in
+// avr_kernels.cu.  No host implementation of the hot path exists here.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/avrecode_b200.h"
+#include "avr_api_internal.h"
+#include "avr_host_tables.h"
+#include "avr_kernels.h"
+#include "avr_record.h"
+
+static thread_local std::string g_err;
+void avr_set_error(const char* fmt, ...) {
+  char buf[512];
+  va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+  g_err = buf;
+}
+extern "C" const char* avr_last_error(void) { return g_err.c_str(); }
+extern "C" int avr_version(void) { return 100; }
+
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { avr_set_error("%s: %s", #x, cudaGetErrorString(e_)); return AVR_E_CUDA; } } while (0)
+
+struct avr_context {
+  int device;
+  cudaStream_t stream;
+  AvrTables* d_tab;
+  cudaEvent_t ev[4];
+};
+
+extern "C" int avr_context_create(int device, avr_context** out) {
+  if (!out) return AVR_E_ARG;
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { avr_set_error("no CUDA device: this library has no CPU path"); return AVR_E_CUDA; }
+  if (device < 0 || device >= n) { avr_set_error("device %d out of range (%d devices)", device, n); return AVR_E_ARG; }
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) { avr_set_error("device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major, prop.minor); return AVR_E_CUDA; }
+  CU(cudaSetDevice(device));
+  avr_context* c = new avr_context();
+  c->device = device;
+  CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (auto& e : c->ev) CU(cudaEventCreate(&e));
+  AvrTables t;
+  avr_fill_tables(&t);
+  CU(cudaMalloc(&c->d_tab, sizeof t));
+  CU(cudaMemcpy(c->d_tab, &t, sizeof t, cudaMemcpyHostToDevice));
+  *out = c;
+  return AVR_OK;
+}
+extern "C" void avr_context_destroy(avr_context* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaFree(c->d_tab);
+  for (auto& e : c->ev) cudaEventDestroy(e);
+  cudaStreamDestroy(c->stream);
+  delete c;
+}
+extern "C" void* avr_context_stream(avr_context* c) { return c ? (void*)c->stream : nullptr; }
+
+// ---- recorder bindings ------------------------------------------------------------------------
+struct avr_record {
+  avr::FileRecord rec;
+  avr::Recorder recorder;
+  avr_record() : recorder(&rec) {}
+};
+const avr::FileRecord* avr_record_view(const avr_record* r) { return &r->rec; }
+avr::FileRecord* avr_record_mut(avr_record* r) { return &r->rec; }
+
+static avr::SliceParams to_sp(const avr_slice_params* p) {
+  avr::SliceParams s;
+  s.slice_type = p->slice_type; s.first_mb = p->first_mb; s.mb_w = p->mb_w; s.mb_h = p->mb_h;
+  s.num_ref[0] = p->num_ref[0]; s.num_ref[1] = p->num_ref[1]; s.cabac_init_idc = p->cabac_init_idc;
+  s.slice_qp = p->slice_qp; s.transform_8x8_mode = p->transform_8x8_mode; s.chroma_format_idc = p->chroma_format_idc;
+  s.direct_8x8_inference = p->direct_8x8_inference;
+  return s;
+}
+static void from_sp(const avr::SliceParams& s, avr_slice_params* p) {
+  p->slice_type = s.slice_type; p->first_mb = s.first_mb; p->mb_w = s.mb_w; p->mb_h = s.mb_h;
+  p->num_ref[0] = s.num_ref[0]; p->num_ref[1] = s.num_ref[1]; p->cabac_init_idc = s.cabac_init_idc;
+  p->slice_qp = s.slice_qp; p->transform_8x8_mode = s.transform_8x8_mode; p->chroma_format_idc = s.chroma_format_idc;
+  p->direct_8x8_inference = s.direct_8x8_inference;
+}
+
+extern "C" avr_record* avr_record_new(void) { return new avr_record(); }
+extern "C" void avr_record_free(avr_record* r) { delete r; }
+extern "C" void avr_rec_frame_spec(avr_record* r, int fn, int w, int h) { r->recorder.frame_spec(fn, w, h); }
+extern "C" void avr_rec_slice_begin(avr_record* r, int coded, uint64_t off, uint32_t size, const avr_slice_params* sp) {
+  r->recorder.slice_begin(coded != 0, off, size, to_sp(sp));
+}
+extern "C" void avr_rec_slice_end(avr_record* r) { r->recorder.slice_end(); }
+extern "C" void avr_rec_mb_xy(avr_record* r, int x, int y) { r->recorder.mb_xy(x, y); }
+extern "C" void avr_rec_begin_sub_mb(avr_record* r, int cat, int n, int mc, int dc, int c422) { r->recorder.begin_sub_mb(cat, n, mc, dc, c422); }
+extern "C" void avr_rec_end_sub_mb(avr_record*) {}
+extern "C" void avr_rec_begin_coding_type(avr_record* r, int ct) { if (ct == 2) r->recorder.begin_sigmap(); }
+extern "C" void avr_rec_end_coding_type(avr_record* r, int ct) { if (ct == 2) r->recorder.end_sigmap(); }
+extern "C" void avr_rec_bin(avr_record* r, int ctx, int sym) { r->recorder.bin(ctx, sym); }
+extern "C" int avr_record_annexb(avr_record* r, const uint8_t* data, size_t n) {
+  if (!r || (!data && n)) return AVR_E_ARG;
+  return avr::record_annexb(data, n, &r->rec);
+}
+extern "C" void avr_record_counts(const avr_record* r, uint64_t c[6]) {
+  c[0] = r->rec.source_bins; c[1] = r->rec.blocks.size(); c[2] = r->rec.slices.size(); c[3] = r->rec.spans.size();
+  c[4] = r->rec.frames.size(); c[5] = (uint64_t)r->rec.out_of_domain;
+}
+uint32_t avr_span_flip(const avr::FileRecord& rec, uint32_t i) {
+  // pictures started since the previous CODED slice of the file
+  const avr::SliceSpan& sp = rec.spans[i];
+  int64_t last = -1;
+  for (uint32_t k = i; k-- > 0;) if (rec.spans[k].slice_index >= 0) { last = rec.spans[k].frame; break; }
+  if (last == (int64_t)sp.frame) return 0;
+  int64_t k = (int64_t)sp.frame - last;
+  return (k == 1 && rec.frames[sp.frame].prev_valid) ? 1u : 2u;
+}
+extern "C" int avr_record_span(const avr_record* r, uint32_t i, uint64_t* off, uint32_t* size, int32_t* slice_index,
+                               uint32_t* flip, avr_slice_params* sp) {
+  if (!r || i >= r->rec.spans.size()) return AVR_E_ARG;
+  const avr::SliceSpan& s = r->rec.spans[i];
+  if (off) *off = s.payload_off;
+  if (size) *size = s.size;
+  if (slice_index) *slice_index = s.slice_index;
+  if (flip) *flip = avr_span_flip(r->rec, i);
+  if (sp) from_sp(s.sp, sp);
+  return AVR_OK;
+}
+
+// ---- device memory helper ---------------------------------------------------------------------
+struct DevMem {
+  std::vector<void*> ptrs;
+  size_t bytes = 0;
+  template <class T> int alloc(T** p, size_t count) {
+    *p = nullptr;
+    size_t n = (count ? count : 1) * sizeof(T) + 64;
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, n);
+    if (e != cudaSuccess) { avr_set_error("cudaMalloc(%zu): %s", n, cudaGetErrorString(e)); return AVR_E_NOMEM; }
+    ptrs.push_back(q); bytes += n; *p = (T*)q;
+    return AVR_OK;
+  }
+  void release() { for (void* p : ptrs) cudaFree(p); ptrs.clear(); bytes = 0; }
+};
+#define TRY(x) do { int r_ = (x); if (r_ != AVR_OK) return r_; } while (0)
+
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
+
+// ---- compress batch ---------------------------------------------------------------------------
+struct avr_cbatch {
+  avr_context* ctx;
+  DevMem mem;
+  AvrDevBatch d;
+  std::vector<uint32_t> file_slice_off;    // per file: first batch-global slice
+  std::vector<uint32_t> h_len; std::vector<int> h_status; std::vector<uint64_t> h_off;
+  std::vector<uint8_t> h_out;
+  uint64_t scratch_bytes = 0, pic_mbs = 0, chain_mbs = 0;
+  bool have_pipe = false, have_chain = false;
+  avr_timing t;
+  bool ran = false, fetched = false;
+  // device-side mutable pointers kept for fetch
+  uint64_t* d_scratch_off = nullptr; uint32_t* d_scratch_cap = nullptr;
+};
+
+extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs, int nfiles, avr_cbatch** out) {
+  if (!ctx || !recs || nfiles < 0 || !out) return AVR_E_ARG;
+  if (nfiles > 1024) { avr_set_error("at most 1024 files per batch (sort key has 10 file bits)"); return AVR_E_ARG; }
+  CU(cudaSetDevice(ctx->device));
+  avr_cbatch* b = new avr_cbatch();
+  b->ctx = ctx;
+  memset(&b->d, 0, sizeof b->d);
+  memset(&b->t, 0, sizeof b->t);
+  std::vector<AvrFileDesc> fds((size_t)nfiles);
+  std::vector<AvrBatchSlice> bsl;
+  std::vector<AvrSlice> sl;
+  std::vector<uint64_t> soff; std::vector<uint32_t> scap;
+  uint64_t nbins = 0, nblocks = 0, nframes = 0, emitted = 0, chain_mbs = 0, pic_mbs = 0, scratch = 0;
+  for (int f = 0; f < nfiles; f++) {
+    const avr::FileRecord& r = recs[f]->rec;
+    if (r.error || r.out_of_domain) { avr_set_error("file %d: record not compressible (error %d, out_of_domain %d)", f, r.error, r.out_of_domain); delete b; return AVR_E_UNSUPPORTED; }
+    AvrFileDesc& fd = fds[f];
+    memset(&fd, 0, sizeof fd);
+    fd.bin_off = nbins; fd.nbins = (uint32_t)r.bins.size();
+    fd.block_off = (uint32_t)nblocks; fd.nblocks = (uint32_t)r.blocks.size();
+    fd.slice_off = (uint32_t)bsl.size(); fd.nslices = (uint32_t)r.slices.size();
+    fd.frame_off = (uint32_t)nframes; fd.nframes = (uint32_t)r.frames.size();
+    fd.pic_mb_base = (uint32_t)pic_mbs;
+    for (auto& fr : r.frames) { uint32_t m = (uint32_t)fr.mb_w * fr.mb_h; if (m > fd.max_mbs) fd.max_mbs = m; pic_mbs += m; }
+    fd.mb_base = (uint32_t)chain_mbs;
+    chain_mbs += 2ull * fd.max_mbs;
+    b->file_slice_off.push_back((uint32_t)bsl.size());
+    for (auto& s : r.slices) {
+      // every coded slice must end with end_of_slice_flag = 1 (recode.cpp:1099-1102)
+      if (s.bin_end <= s.bin_start || AVR_BIN_CTX(r.bins[s.bin_end - 1]) != AVR_CTX_TERMINATE || !AVR_BIN_SYM(r.bins[s.bin_end - 1])) {
+        avr_set_error("file %d: slice without terminating bin", f); delete b; return AVR_E_CORRUPT;
+      }
+      AvrBatchSlice bs = {(uint32_t)f, s.bin_start, s.bin_end, s.block_start + fd.block_off, s.block_end + fd.block_off};
+      bsl.push_back(bs); sl.push_back(s);
+      uint32_t cap = (s.bin_end - s.bin_start) + 6 * (s.block_end - s.block_start) + 16;
+      soff.push_back(scratch); scap.push_back(cap); scratch += (cap + 15) & ~15ull;
+    }
+    nbins += r.bins.size(); nblocks += r.blocks.size(); nframes += r.frames.size(); emitted += r.emitted;
+    b->t.bins += r.source_bins;
+  }
+  if (emitted >= (1ull << 31) || nblocks + bsl.size() >= (1ull << 31) || pic_mbs >= (1ull << 32) || chain_mbs >= (1ull << 32)) {
+    avr_set_error("batch too large for one launch (%llu coded symbols); split it", (unsigned long long)emitted); delete b; return AVR_E_ARG;
+  }
+  b->file_slice_off.push_back((uint32_t)bsl.size());
+  b->t.coded_symbols = emitted;
+  b->scratch_bytes = scratch;
+  b->pic_mbs = pic_mbs; b->chain_mbs = chain_mbs;
+  AvrDevBatch& d = b->d;
+  d.nfiles = nfiles; d.nslices = (uint32_t)bsl.size(); d.nblocks = (uint32_t)nblocks; d.nbins = nbins;
+  d.emit_cap = (uint32_t)emitted; d.tab = ctx->d_tab;
+  int fb = 0; while ((1 << fb) < nfiles) fb++;
+  d.sort_end_bit = 22 + fb;
+  // allocate
+  AvrFileDesc* d_fds; uint16_t* d_bins; AvrBlock* d_blocks; AvrSlice* d_sl; AvrBatchSlice* d_bsl; AvrFrame* d_frames;
+  DevMem& m = b->mem;
+  int rc = AVR_OK;
+  auto fail = [&](int r) { m.release(); delete b; return r; };
+  if ((rc = m.alloc(&d_fds, fds.size())) || (rc = m.alloc(&d_bins, nbins)) || (rc = m.alloc(&d_blocks, nblocks)) ||
+      (rc = m.alloc(&d_sl, sl.size())) || (rc = m.alloc(&d_bsl, bsl.size())) || (rc = m.alloc(&d_frames, nframes)) ||
+      (rc = m.alloc(&b->d_scratch_off, soff.size())) || (rc = m.alloc(&b->d_scratch_cap, scap.size())) ||
+      (rc = m.alloc(&d.scratch, scratch)) || (rc = m.alloc(&d.out_len, bsl.size())) || (rc = m.alloc(&d.status, bsl.size())) ||
+      (rc = m.alloc(&d.out_off, bsl.size())) || (rc = m.alloc(&d.out_total, 1)) || (rc = m.alloc(&d.out, scratch)))
+    return fail(rc);
+  d.fds = d_fds; d.bins = d_bins; d.blocks = d_blocks; d.slices = d_sl; d.bslices = d_bsl; d.frames = d_frames;
+  d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
+  // upload (timed: this is the H2D leg of the e2e number)
+  cudaStream_t st = ctx->stream;
+  cudaEventRecord(ctx->ev[0], st);
+  uint64_t h2d = 0;
+  auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };
+  up(d_fds, fds.data(), fds.size() * sizeof(AvrFileDesc));
+  for (int f = 0; f < nfiles; f++) {
+    const avr::FileRecord& r = recs[f]->rec;
+    up(d_bins + fds[f].bin_off, r.bins.data(), r.bins.size() * sizeof(uint16_t));
+    up(d_blocks + fds[f].block_off, r.blocks.data(), r.blocks.size() * sizeof(AvrBlock));
+    up(d_frames + fds[f].frame_off, r.frames.data(), r.frames.size() * sizeof(AvrFrame));
+  }
+  up(d_sl, sl.data(), sl.size() * sizeof(AvrSlice));
+  up(d_bsl, bsl.data(), bsl.size() * sizeof(AvrBatchSlice));
+  up(b->d_scratch_off, soff.data(), soff.size() * sizeof(uint64_t));
+  up(b->d_scratch_cap, scap.data(), scap.size() * sizeof(uint32_t));
+  cudaEventRecord(ctx->ev[1], st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { avr_set_error("upload: %s", cudaGetErrorString(e)); return fail(AVR_E_CUDA); }
+  b->t.h2d_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
+  b->t.h2d_bytes = h2d;
+  b->h_off = soff;   // reused as host copy of scratch offsets until fetch overwrites
+  *out = b;
+  return AVR_OK;
+}
+
+extern "C" int avr_cbatch_run(avr_cbatch* b, int mode) {
+  if (!b) return AVR_E_ARG;
+  avr_context* ctx = b->ctx;
+  CU(cudaSetDevice(ctx->device));
+  AvrDevBatch& d = b->d;
+  DevMem& m = b->mem;
+  cudaStream_t st = ctx->stream;
+  if (mode == AVR_MODE_PIPELINE && !b->have_pipe) {
+    const uint32_t n = d.emit_cap, nent = d.nblocks + d.nslices;
+    d.pic_store_bytes = (size_t)b->pic_mbs * AVR_MB_STRIDE + 64;
+    d.cub_tmp_bytes = avr_pipeline_tmp_bytes(n, nent, d.sort_end_bit);
+    uint8_t* tmp;
+    TRY(m.alloc(&d.pic_store, d.pic_store_bytes)); TRY(m.alloc(&d.seg, (size_t)nent + 1));
+    TRY(m.alloc(&d.keys_a, n)); TRY(m.alloc(&d.keys_b, n)); TRY(m.alloc(&d.idx_a, n)); TRY(m.alloc(&d.idx_b, n));
+    TRY(m.alloc(&d.head, n)); TRY(m.alloc(&d.psum, n)); TRY(m.alloc(&d.fn, n)); TRY(m.alloc(&d.prob, n));
+    TRY(m.alloc(&tmp, d.cub_tmp_bytes)); d.cub_tmp = tmp;
+    b->have_pipe = true;
+  }
+  if (mode == AVR_MODE_CHAIN && !b->have_chain) {
+    TRY(m.alloc(&d.est_pool, (size_t)d.nfiles * AVR_KEY_COUNT));
+    TRY(m.alloc(&d.store_pool, (size_t)b->chain_mbs * AVR_MB_STRIDE + 64));
+    b->have_chain = true;
+  }
+  int launches = 0, rc;
+  cudaEventRecord(ctx->ev[0], st);
+  if (mode == AVR_MODE_CHAIN) {
+    CU(cudaMemsetAsync(d.est_pool, 0x01, (size_t)d.nfiles * AVR_KEY_COUNT * sizeof(uint16_t), st));   // pos = neg = 1
+    cudaEventRecord(ctx->ev[2], st);
+    rc = avr_launch_compress_chain(d, st); launches = 1;
+    cudaEventRecord(ctx->ev[3], st);
+  } else if (mode == AVR_MODE_PIPELINE) {
+    rc = avr_launch_compress_pipeline(d, st, &launches, ctx->ev[2], ctx->ev[3]);
+  } else return AVR_E_ARG;
+  if (rc) { avr_set_error("compress launch: %s", cudaGetErrorString((cudaError_t)rc)); return AVR_E_CUDA; }
+  rc = avr_launch_compact(d.scratch, d.scratch_off, d.out_len, d.out_off, d.out_total, d.out, d.nslices, st); launches += 2;
+  if (rc) { avr_set_error("compact launch: %s", cudaGetErrorString((cudaError_t)rc)); return AVR_E_CUDA; }
+  cudaEventRecord(ctx->ev[1], st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { avr_set_error("compress kernels: %s", cudaGetErrorString(e)); return AVR_E_CUDA; }
+  b->t.kernel_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
+  b->t.coder_launch_ms_x1000 = (uint32_t)(ev_ms(ctx->ev[2], ctx->ev[3]) * 1000.0f);
+  b->t.launches = (uint32_t)launches;
+  b->ran = true; b->fetched = false;
+  return AVR_OK;
+}
+
+extern "C" int avr_cbatch_fetch(avr_cbatch* b) {
+  if (!b || !b->ran) return AVR_E_ARG;
+  avr_context* ctx = b->ctx;
+  CU(cudaSetDevice(ctx->device));
+  AvrDevBatch& d = b->d;
+  cudaStream_t st = ctx->stream;
+  const size_t ns = d.nslices;
+  b->h_len.resize(ns); b->h_status.resize(ns); b->h_off.resize(ns);
+  uint64_t total = 0;
+  cudaEventRecord(ctx->ev[0], st);
+  if (ns) {
+    cudaMemcpyAsync(b->h_len.data(), d.out_len, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(b->h_status.data(), d.status, ns * sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(b->h_off.data(), d.out_off, ns * sizeof(uint64_t), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&total, d.out_total, sizeof total, cudaMemcpyDeviceToHost, st);
+    CU(cudaStreamSynchronize(st));
+    if (total > b->scratch_bytes) { avr_set_error("payload total %llu exceeds scratch", (unsigned long long)total); return AVR_E_OVERFLOW; }
+    b->h_out.resize(total);
+    if (total) cudaMemcpyAsync(b->h_out.data(), d.out, total, cudaMemcpyDeviceToHost, st);
+  }
+  cudaEventRecord(ctx->ev[1], st);
+  CU(cudaStreamSynchronize(st));
+  b->t.d2h_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
+  b->t.d2h_bytes = total + ns * 16 + 8;
+  for (size_t s = 0; s < ns; s++)
+    if (b->h_status[s]) { avr_set_error("slice %zu: device status %d", s, b->h_status[s]); return b->h_status[s]; }
+  b->fetched = true;
+  return AVR_OK;
+}
+
+extern "C" int avr_cbatch_payload(const avr_cbatch* b, int file, uint32_t slice, const uint8_t** data, uint32_t* len) {
+  if (!b || !b->fetched || file < 0 || file >= b->d.nfiles) return AVR_E_ARG;
+  uint32_t s = b->file_slice_off[file] + slice;
+  if (s >= b->file_slice_off[file + 1]) return AVR_E_ARG;
+  *data = b->h_out.data() + b->h_off[s];
+  *len = b->h_len[s];
+  return AVR_OK;
+}
+extern "C" void avr_cbatch_timing(const avr_cbatch* b, avr_timing* t) { if (b && t) *t = b->t; }
+extern "C" void avr_cbatch_destroy(avr_cbatch* b) {
+  if (!b) return;
+  cudaSetDevice(b->ctx->device);
+  b->mem.release();
+  delete b;
+}
+
+// ---- decompress batch -------------------------------------------------------------------------
+struct avr_dbatch {
+  avr_context* ctx;
+  DevMem mem;
+  AvrDevDBatch d;
+  std::vector<uint64_t> out_off; std::vector<uint32_t> out_cap;
+  std::vector<uint32_t> h_len, h_bins; std::vector<int> h_status;
+  std::vector<uint8_t> h_out;
+  uint64_t out_bytes = 0;
+  avr_timing t;
+  bool ran = false, fetched = false;
+};
+
+extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, const uint32_t* per_file, int nfiles, avr_dbatch** out) {
+  if (!ctx || (!slices && nfiles) || !per_file || nfiles < 0 || !out) return AVR_E_ARG;
+  CU(cudaSetDevice(ctx->device));
+  avr_dbatch* b = new avr_dbatch();
+  b->ctx = ctx;
+  memset(&b->d, 0, sizeof b->d);
+  memset(&b->t, 0, sizeof b->t);
+  std::vector<AvrFileDesc> fds((size_t)nfiles);
+  std::vector<AvrDecSlice> ds;
+  uint64_t pay = 0, outb = 0, chain_mbs = 0;
+  uint32_t s = 0;
+  for (int f = 0; f < nfiles; f++) {
+    AvrFileDesc& fd = fds[f];
+    memset(&fd, 0, sizeof fd);
+    fd.slice_off = s; fd.nslices = per_file[f];
+    for (uint32_t k = 0; k < per_file[f]; k++, s++) {
+      const avr_dslice& in = slices[s];
+      if (in.sp.mb_w <= 0 || in.sp.mb_h <= 0 || in.sp.mb_w > 1024 || in.sp.mb_h > 1024 || (!in.payload && in.payload_len)) {
+        avr_set_error("slice %u: bad parameters", s); delete b; return AVR_E_ARG;
+      }
+      if (k == 0 && in.flip == 0) { avr_set_error("slice %u: first slice of a file must start a picture", s); delete b; return AVR_E_ARG; }
+      AvrDecSlice d;
+      memset(&d, 0, sizeof d);
+      d.payload_off = pay; d.payload_len = in.payload_len; pay += ((uint64_t)in.payload_len + 15) & ~15ull;
+      d.out_off = outb; d.out_cap = in.size + 64; outb += ((uint64_t)d.out_cap + 15) & ~15ull;
+      d.flip = in.flip; d.sp = to_sp(&in.sp);
+      uint32_t mbs = (uint32_t)in.sp.mb_w * (uint32_t)in.sp.mb_h;
+      if (mbs > fd.max_mbs) fd.max_mbs = mbs;
+      ds.push_back(d);
+      b->out_off.push_back(d.out_off); b->out_cap.push_back(d.out_cap);
+    }
+    fd.mb_base = (uint32_t)chain_mbs;
+    chain_mbs += 2ull * (fd.max_mbs > 1024 ? fd.max_mbs : 1024);   // also hosts the file's MbInfo row (mb_w <= 1024)
+  }
+  if (chain_mbs >= (1ull << 32)) { avr_set_error("batch too large"); delete b; return AVR_E_ARG; }
+  b->out_bytes = outb;
+  AvrDevDBatch& d = b->d;
+  DevMem& m = b->mem;
+  d.nfiles = nfiles; d.nslices = (uint32_t)ds.size(); d.tab = ctx->d_tab;
+  AvrFileDesc* d_fds; AvrDecSlice* d_ds; uint8_t* d_pay;
+  int rc;
+  auto fail = [&](int r) { m.release(); delete b; return r; };
+  if ((rc = m.alloc(&d_fds, fds.size())) || (rc = m.alloc(&d_ds, ds.size())) || (rc = m.alloc(&d_pay, pay + 16)) ||
+      (rc = m.alloc(&d.est_pool, (size_t)nfiles * AVR_KEY_COUNT)) || (rc = m.alloc(&d.store_pool, (size_t)chain_mbs * AVR_MB_STRIDE)) ||
+      (rc = m.alloc(&d.row_pool, (size_t)chain_mbs)) || (rc = m.alloc(&d.out, outb)) || (rc = m.alloc(&d.out_len, ds.size())) ||
+      (rc = m.alloc(&d.out_bins, ds.size())) || (rc = m.alloc(&d.status, ds.size())))
+    return fail(rc);
+  d.fds = d_fds; d.slices = d_ds; d.payloads = d_pay;
+  cudaStream_t st = ctx->stream;
+  cudaEventRecord(ctx->ev[0], st);
+  uint64_t h2d = 0;
+  auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };
+  up(d_fds, fds.data(), fds.size() * sizeof(AvrFileDesc));
+  up(d_ds, ds.data(), ds.size() * sizeof(AvrDecSlice));
+  for (size_t i = 0; i < ds.size(); i++) up(d_pay + ds[i].payload_off, slices[i].payload, slices[i].payload_len);
+  cudaEventRecord(ctx->ev[1], st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { avr_set_error("upload: %s", cudaGetErrorString(e)); return fail(AVR_E_CUDA); }
+  b->t.h2d_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
+  b->t.h2d_bytes = h2d;
+  *out = b;
+  return AVR_OK;
+}
+
+extern "C" int avr_dbatch_run(avr_dbatch* b) {
+  if (!b) return AVR_E_ARG;
+  avr_context* ctx = b->ctx;
+  CU(cudaSetDevice(ctx->device));
+  AvrDevDBatch& d = b->d;
+  cudaStream_t st = ctx->stream;
+  cudaEventRecord(ctx->ev[0], st);
+  CU(cudaMemsetAsync(d.est_pool, 0x01, (size_t)d.nfiles * AVR_KEY_COUNT * sizeof(uint16_t), st));
+  cudaEventRecord(ctx->ev[2], st);
+  int rc = avr_launch_decompress_chain(d, st);
+  cudaEventRecord(ctx->ev[3], st);
+  if (rc) { avr_set_error("decompress launch: %s", cudaGetErrorString((cudaError_t)rc)); return AVR_E_CUDA; }
+  cudaEventRecord(ctx->ev[1], st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { avr_set_error("decompress kernel: %s", cudaGetErrorString(e)); return AVR_E_CUDA; }
+  b->t.kernel_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
+  b->t.coder_launch_ms_x1000 = (uint32_t)(ev_ms(ctx->ev[2], ctx->ev[3]) * 1000.0f);
+  b->t.launches = 1;
+  b->ran = true; b->fetched = false;
+  return AVR_OK;
+}
+
+extern "C" int avr_dbatch_fetch(avr_dbatch* b) {
+  if (!b || !b->ran) return AVR_E_ARG;
+  avr_context* ctx = b->ctx;
+  CU(cudaSetDevice(ctx->device));
+  AvrDevDBatch& d = b->d;
+  cudaStream_t st = ctx->stream;
+  const size_t ns = d.nslices;
+  b->h_len.resize(ns); b->h_bins.resize(ns); b->h_status.resize(ns); b->h_out.resize(b->out_bytes);
+  cudaEventRecord(ctx->ev[0], st);
+  if (ns) {
+    cudaMemcpyAsync(b->h_len.data(), d.out_len, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(b->h_bins.data(), d.out_bins, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(b->h_status.data(), d.status, ns * sizeof(int), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(b->h_out.data(), d.out, b->out_bytes, cudaMemcpyDeviceToHost, st);
+  }
+  cudaEventRecord(ctx->ev[1], st);
+  CU(cudaStreamSynchronize(st));
+  b->t.d2h_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
+  b->t.d2h_bytes = b->out_bytes + ns * 12;
+  b->t.bins = 0;
+  for (size_t s = 0; s < ns; s++) {
+    b->t.bins += b->h_bins[s];
+    if (b->h_status[s]) { avr_set_error("slice %zu: device status %d", s, b->h_status[s]); return b->h_status[s]; }
+  }
+  b->fetched = true;
+  return AVR_OK;
+}
+
+extern "C" int avr_dbatch_slice(const avr_dbatch* b, uint32_t slice, const uint8_t** data, uint32_t* len, uint32_t* bins) {
+  if (!b || !b->fetched || slice >= b->d.nslices) return AVR_E_ARG;
+  if (data) *data = b->h_out.data() + b->out_off[slice];
+  if (len) *len = b->h_len[slice];
+  if (bins) *bins = b->h_bins[slice];
+  return AVR_OK;
+}
+extern "C" void avr_dbatch_timing(const avr_dbatch* b, avr_timing* t) { if (b && t) *t = b->t; }
+extern "C" void avr_dbatch_destroy(avr_dbatch* b) {
+  if (!b) return;
+  cudaSetDevice(b->ctx->device);
+  b->mem.release();
+  delete b;
+}

@@ -1,0 +1,9 @@
+// Internal C++ glue shared by avr_api.cu and avr_files.cpp (not part of the C ABI).
+#pragma once
+#include <stdint.h>
+#include "avr_record.h"
+struct avr_record;
+void avr_set_error(const char* fmt, ...);
+const avr::FileRecord* avr_record_view(const avr_record* r);
+avr::FileRecord* avr_record_mut(avr_record* r);
+uint32_t avr_span_flip(const avr::FileRecord& rec, uint32_t span_index);

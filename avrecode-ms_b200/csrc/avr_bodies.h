@@ -23,7 +23,7 @@ struct AvrFileDesc {
   uint32_t slice_off, nslices;       // into slices[] (compress) / dec_slices[] (decompress)
   uint32_t frame_off, nframes;       // into frames[]
   uint32_t max_mbs;                  // largest picture of the file, in macroblocks
-  uint32_t mb_base;                  // chain kernels: first macroblock slot of this file (2*max_mbs slots per file)
+  uint32_t mb_base;                  // chain kernels: first macroblock slot of this file (a file owns 2*max_mbs slots)
   uint32_t pic_mb_base;              // pipeline: first macroblock slot of this file's per-picture stores
 };
 

@@ -1,0 +1,331 @@
+// File-level drop-in for `recode compress` / `recode decompress` on memory buffers: the
+// recode.proto container (reference recode.proto:1-19; block sequence rules recode.cpp:1282-1304,
+// 1129-1131; reader rules recode.cpp:1366-1416; x264 padding patch recode.cpp:1352-1362) around
+// the device batches of avr_api.cu.  Host work here is framing only -- every bin is coded on
+// the GPU.
+#include <string.h>
+#include <algorithm>
+#include <atomic>
+#include <string>
+#include <thread>
+#include <vector>
+#include "../../include/avrecode_b200.h"
+#include "avr_api_internal.h"
+
+namespace {
+
+// ---- proto2 wire writer (fields in tag order, set-but-empty fields are emitted) ----------------
+void put_varint(std::vector<uint8_t>& o, uint64_t v) {
+  while (v >= 0x80) { o.push_back((uint8_t)(v | 0x80)); v >>= 7; }
+  o.push_back((uint8_t)v);
+}
+size_t varint_len(uint64_t v) { size_t n = 1; while (v >= 0x80) { v >>= 7; n++; } return n; }
+void put_bytes_field(std::vector<uint8_t>& o, uint8_t tag, const uint8_t* p, size_t n) {
+  o.push_back(tag); put_varint(o, n); o.insert(o.end(), p, p + n);
+}
+void put_block_literal(std::vector<uint8_t>& o, const uint8_t* p, size_t n) {
+  o.push_back(0x12); put_varint(o, 1 + varint_len(n) + n);
+  put_bytes_field(o, 0x12, p, n);
+}
+void put_block_skip(std::vector<uint8_t>& o, uint64_t size) {
+  o.push_back(0x12); put_varint(o, 1 + varint_len(size) + 2);
+  o.push_back(0x08); put_varint(o, size);
+  o.push_back(0x18); o.push_back(0x01);
+}
+void put_block_cabac(std::vector<uint8_t>& o, uint64_t size, const uint8_t* cabac, size_t n, int parity, const uint8_t* last_byte) {
+  size_t body = 1 + varint_len(size) + 1 + varint_len(n) + n + 2 + (last_byte ? 3 : 0);
+  o.push_back(0x12); put_varint(o, body);
+  o.push_back(0x08); put_varint(o, size);
+  put_bytes_field(o, 0x22, cabac, n);
+  o.push_back(0x28); o.push_back((uint8_t)parity);
+  if (last_byte) { o.push_back(0x32); o.push_back(0x01); o.push_back(*last_byte); }
+}
+
+// ---- reader -----------------------------------------------------------------------------------
+struct Block {
+  bool has_size = false, has_literal = false, has_skip = false, has_cabac = false, has_parity = false, has_last = false;
+  uint64_t size = 0; bool skip = false; int parity = 0;
+  const uint8_t* literal = nullptr; size_t literal_len = 0;
+  const uint8_t* cabac = nullptr; size_t cabac_len = 0;
+  const uint8_t* last = nullptr; size_t last_len = 0;
+};
+bool get_varint(const uint8_t* p, size_t n, size_t& i, uint64_t* v) {
+  uint64_t r = 0; int sh = 0;
+  while (i < n && sh < 64) {
+    uint8_t b = p[i++];
+    r |= (uint64_t)(b & 0x7F) << sh; sh += 7;
+    if (!(b & 0x80)) { *v = r; return true; }
+  }
+  return false;
+}
+bool skip_field(const uint8_t* p, size_t n, size_t& i, int wt) {
+  uint64_t v;
+  switch (wt) {
+    case 0: return get_varint(p, n, i, &v);
+    case 1: if (i + 8 > n) return false; i += 8; return true;
+    case 2: if (!get_varint(p, n, i, &v) || v > n - i) return false; i += (size_t)v; return true;
+    case 5: if (i + 4 > n) return false; i += 4; return true;
+    default: return false;
+  }
+}
+bool parse_container(const uint8_t* p, size_t n, std::vector<Block>* blocks) {
+  size_t i = 0;
+  while (i < n) {
+    uint64_t tag, len;
+    if (!get_varint(p, n, i, &tag)) return false;
+    if ((tag >> 3) != 2 || (tag & 7) != 2) { if (!skip_field(p, n, i, (int)(tag & 7))) return false; continue; }
+    if (!get_varint(p, n, i, &len) || len > n - i) return false;
+    const uint8_t* b = p + i; size_t bn = (size_t)len, j = 0;
+    i += bn;
+    Block blk;
+    while (j < bn) {
+      uint64_t t, v;
+      if (!get_varint(b, bn, j, &t)) return false;
+      int f = (int)(t >> 3), wt = (int)(t & 7);
+      if (wt == 0 && (f == 1 || f == 3 || f == 5)) {
+        if (!get_varint(b, bn, j, &v)) return false;
+        if (f == 1) { blk.has_size = true; blk.size = v; }
+        else if (f == 3) { blk.has_skip = true; blk.skip = v != 0; }
+        else { blk.has_parity = true; blk.parity = v != 0; }
+      } else if (wt == 2 && (f == 2 || f == 4 || f == 6)) {
+        if (!get_varint(b, bn, j, &v) || v > bn - j) return false;
+        if (f == 2) { blk.has_literal = true; blk.literal = b + j; blk.literal_len = (size_t)v; }
+        else if (f == 4) { blk.has_cabac = true; blk.cabac = b + j; blk.cabac_len = (size_t)v; }
+        else { blk.has_last = true; blk.last = b + j; blk.last_len = (size_t)v; }
+        j += (size_t)v;
+      } else if (!skip_field(b, bn, j, wt)) return false;
+    }
+    blocks->push_back(blk);
+  }
+  return true;
+}
+
+template <class F>
+void parallel_for(int n, int threads, F&& f) {
+  if (threads <= 1 || n <= 1) { for (int i = 0; i < n; i++) f(i); return; }
+  std::atomic<int> next(0);
+  std::vector<std::thread> th;
+  for (int t = 0; t < std::min(threads, n); t++)
+    th.emplace_back([&] { for (int i; (i = next.fetch_add(1)) < n;) f(i); });
+  for (auto& t : th) t.join();
+}
+
+void add_timing(avr_timing* acc, const avr_timing& t) {
+  acc->h2d_ms += t.h2d_ms; acc->kernel_ms += t.kernel_ms; acc->d2h_ms += t.d2h_ms;
+  acc->h2d_bytes += t.h2d_bytes; acc->d2h_bytes += t.d2h_bytes; acc->bins += t.bins;
+  acc->coded_symbols += t.coded_symbols; acc->launches += t.launches; acc->coder_launch_ms_x1000 += t.coder_launch_ms_x1000;
+}
+
+bool to_buffer(const std::vector<uint8_t>& v, avr_buffer* b) {
+  b->size = v.size();
+  b->data = (uint8_t*)malloc(v.size() ? v.size() : 1);
+  if (!b->data) return false;
+  if (!v.empty()) memcpy(b->data, v.data(), v.size());
+  return true;
+}
+
+}  // namespace
+
+extern "C" void avr_buffer_free(avr_buffer* b) { if (b) { free(b->data); b->data = nullptr; b->size = 0; } }
+
+// compressor::run (recode.cpp:1122-1132) for n files at once.
+extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
+                                  avr_buffer* out, avr_timing* tacc) {
+  if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
+  avr_timing tt; memset(&tt, 0, sizeof tt);
+  std::vector<avr_record*> recs((size_t)n, nullptr);
+  std::vector<int> rec_rc((size_t)n, 0);
+  parallel_for(n, host_threads, [&](int i) {
+    recs[i] = avr_record_new();
+    rec_rc[i] = avr_record_annexb(recs[i], in[i], in_len[i]);
+    if (avr_record_view(recs[i])->out_of_domain) rec_rc[i] = AVR_E_UNSUPPORTED;
+  });
+  auto cleanup = [&]() { for (auto r : recs) avr_record_free(r); };
+  // batches: at most 1024 files and 2^29 coded symbols each
+  std::vector<std::vector<uint8_t>> containers((size_t)n);
+  int rc = AVR_OK;
+  int i0 = 0;
+  while (i0 < n && rc == AVR_OK) {
+    std::vector<int> files;
+    uint64_t sym = 0;
+    int i = i0;
+    for (; i < n && files.size() < 1024; i++) {
+      if (rec_rc[i]) continue;
+      uint64_t e = avr_record_view(recs[i])->emitted;
+      if (!files.empty() && sym + e > (1ull << 29)) break;
+      files.push_back(i); sym += e;
+    }
+    i0 = i;
+    if (files.empty()) continue;
+    std::vector<const avr_record*> br;
+    for (int f : files) br.push_back(recs[f]);
+    avr_cbatch* b = nullptr;
+    rc = avr_cbatch_create(ctx, br.data(), (int)br.size(), &b);
+    if (rc == AVR_OK) rc = avr_cbatch_run(b, AVR_MODE_PIPELINE);
+    if (rc == AVR_OK) rc = avr_cbatch_fetch(b);
+    if (rc == AVR_OK) {
+      avr_timing t; avr_cbatch_timing(b, &t); add_timing(&tt, t);
+      // containers of this batch (recode.cpp:1282-1304 block sequence)
+      parallel_for((int)files.size(), host_threads, [&](int k) {
+        const int f = files[k];
+        const avr::FileRecord& r = *avr_record_view(recs[f]);
+        std::vector<uint8_t>& o = containers[f];
+        o.reserve(in_len[f] + in_len[f] / 16 + 64);
+        size_t prev_end = 0;
+        for (const avr::SliceSpan& sp : r.spans) {
+          if (sp.slice_index < 0) { put_block_skip(o, sp.size); continue; }
+          put_block_literal(o, in[f] + prev_end, (size_t)sp.payload_off - prev_end);
+          prev_end = (size_t)sp.payload_off + sp.size;
+          const uint8_t* p; uint32_t len;
+          avr_cbatch_payload(b, k, (uint32_t)sp.slice_index, &p, &len);
+          put_block_cabac(o, sp.size, p, len, (int)(sp.size & 1), sp.size > 1 ? in[f] + prev_end - 1 : nullptr);
+        }
+        put_block_literal(o, in[f] + prev_end, in_len[f] - prev_end);
+      });
+    }
+    avr_cbatch_destroy(b);
+  }
+  if (rc != AVR_OK) { cleanup(); return rc; }
+  for (int f = 0; f < n; f++) {
+    // streams the device path does not cover (CAVLC, B/field/MBAFF, 4:2:2+, I_PCM, repeated frame_num)
+    // are stored whole as one literal block: a valid container that restores the input.
+    if (rec_rc[f]) { containers[f].clear(); put_block_literal(containers[f], in[f], in_len[f]); }
+    if (!to_buffer(containers[f], &out[f])) { cleanup(); return AVR_E_NOMEM; }
+  }
+  cleanup();
+  if (tacc) *tacc = tt;
+  return AVR_OK;
+}
+
+// decompressor::run (recode.cpp:1345-1364) for n containers at once.
+namespace {
+struct DFile {
+  std::vector<Block> blocks;
+  std::vector<uint8_t> surrogate;             // literals + 'X' placeholders (recode.cpp:1534-1551 uses marker + 'X')
+  std::vector<avr_dslice> slices;             // coded slices in decode order
+  std::vector<int> slice_block;               // block index of each
+  int rc = AVR_OK;
+};
+}  // namespace
+
+extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
+                                    avr_buffer* out, avr_timing* tacc) {
+  if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
+  avr_timing tt; memset(&tt, 0, sizeof tt);
+  std::vector<DFile> files((size_t)n);
+  parallel_for(n, host_threads, [&](int f) {
+    DFile& d = files[f];
+    if (!parse_container(in[f], in_len[f], &d.blocks)) { d.rc = AVR_E_CORRUPT; return; }
+    std::vector<size_t> coded_pos; std::vector<int> coded_blk;
+    size_t total = 0;
+    for (auto& b : d.blocks) total += b.has_literal ? b.literal_len : b.has_cabac ? (size_t)b.size : 0;
+    d.surrogate.reserve(total);
+    for (size_t i = 0; i < d.blocks.size(); i++) {
+      const Block& b = d.blocks[i];
+      if ((int)b.has_literal + (int)b.has_cabac + (int)b.has_skip != 1) { d.rc = AVR_E_CORRUPT; return; }   // recode.cpp:1371-1373
+      if (b.has_literal) d.surrogate.insert(d.surrogate.end(), b.literal, b.literal + b.literal_len);
+      else if (b.has_cabac) {
+        if (!b.has_size || b.size > (1u << 30)) { d.rc = AVR_E_CORRUPT; return; }                          // recode.cpp:1384-1386
+        coded_pos.push_back(d.surrogate.size()); coded_blk.push_back((int)i);
+        d.surrogate.insert(d.surrogate.end(), (size_t)b.size, (uint8_t)'X');
+      } else if (b.skip) { coded_pos.push_back((size_t)-1); coded_blk.push_back((int)i); }
+      else { d.rc = AVR_E_CORRUPT; return; }
+    }
+    bool any_cabac = false;
+    for (auto& b : d.blocks) any_cabac |= b.has_cabac;
+    if (!any_cabac) return;
+    size_t next = 0;
+    bool have = false; int w = 0, h = 0, fnum = 0;
+    int nflips = 0; bool last_prev_valid = false;
+    int rc = avr::scan_annexb_slices(d.surrogate.data(), d.surrogate.size(), [&](const avr::SliceLoc& loc) -> int {
+      const avr::SliceHeaderInfo& sh = loc.sh;
+      if (sh.sp.first_mb == 0 && !(have && sh.sp.mb_w == w && sh.sp.mb_h == h && sh.frame_num == fnum)) {   // update_frame_spec
+        last_prev_valid = have && sh.sp.mb_w == w && sh.sp.mb_h == h;
+        nflips++;
+        have = true; w = sh.sp.mb_w; h = sh.sp.mb_h; fnum = sh.frame_num;
+      }
+      if (next >= coded_blk.size()) return AVR_E_CORRUPT;
+      const Block& b = d.blocks[coded_blk[next]];
+      const size_t pos = coded_pos[next];
+      next++;
+      if (b.has_skip) return b.size == loc.size ? 0 : AVR_E_CORRUPT;              // recode.cpp:1573-1575
+      if (pos != loc.raw_off || b.size != loc.size) return AVR_E_CORRUPT;          // recode.cpp:1564-1566
+      avr_dslice s;
+      memset(&s, 0, sizeof s);
+      s.payload = b.cabac; s.payload_len = (uint32_t)b.cabac_len; s.size = (uint32_t)b.size;
+      s.flip = nflips == 0 ? 0u : (nflips == 1 && last_prev_valid) ? 1u : 2u;
+      nflips = 0;
+      s.sp.slice_type = sh.sp.slice_type; s.sp.first_mb = sh.sp.first_mb; s.sp.mb_w = sh.sp.mb_w; s.sp.mb_h = sh.sp.mb_h;
+      s.sp.num_ref[0] = sh.sp.num_ref[0]; s.sp.num_ref[1] = sh.sp.num_ref[1]; s.sp.cabac_init_idc = sh.sp.cabac_init_idc;
+      s.sp.slice_qp = sh.sp.slice_qp; s.sp.transform_8x8_mode = sh.sp.transform_8x8_mode;
+      s.sp.chroma_format_idc = sh.sp.chroma_format_idc; s.sp.direct_8x8_inference = sh.sp.direct_8x8_inference;
+      d.slices.push_back(s); d.slice_block.push_back(coded_blk[next - 1]);
+      return 0;
+    });
+    if (rc) { d.rc = rc; return; }
+    for (; next < coded_blk.size(); next++)
+      if (d.blocks[coded_blk[next]].has_cabac) { d.rc = AVR_E_CORRUPT; return; }   // "Not all blocks were decoded."
+  });
+  for (int f = 0; f < n; f++)
+    if (files[f].rc) { avr_set_error("container %d: invalid (%d)", f, files[f].rc); return files[f].rc; }
+
+  std::vector<std::vector<std::vector<uint8_t>>> decoded((size_t)n);   // [file][slice] bytes after the padding patch
+  for (int f = 0; f < n; f++) decoded[f].resize(files[f].slices.size());
+  int rc = AVR_OK;
+  int f0 = 0;
+  while (f0 < n && rc == AVR_OK) {
+    std::vector<avr_dslice> sl; std::vector<uint32_t> per; std::vector<int> ids;
+    uint64_t bytes = 0;
+    int f = f0;
+    for (; f < n && ids.size() < 4096; f++) {
+      if (files[f].slices.empty()) continue;
+      uint64_t fb = 0; for (auto& s : files[f].slices) fb += s.payload_len + s.size;
+      if (!ids.empty() && bytes + fb > (8ull << 30)) break;
+      ids.push_back(f); per.push_back((uint32_t)files[f].slices.size()); bytes += fb;
+      sl.insert(sl.end(), files[f].slices.begin(), files[f].slices.end());
+    }
+    f0 = f;
+    if (ids.empty()) continue;
+    avr_dbatch* b = nullptr;
+    rc = avr_dbatch_create(ctx, sl.data(), per.data(), (int)ids.size(), &b);
+    if (rc == AVR_OK) rc = avr_dbatch_run(b);
+    if (rc == AVR_OK) rc = avr_dbatch_fetch(b);
+    if (rc == AVR_OK) {
+      avr_timing t; avr_dbatch_timing(b, &t); add_timing(&tt, t);
+      uint32_t g = 0;
+      for (size_t k = 0; k < ids.size(); k++) {
+        DFile& d = files[ids[k]];
+        for (size_t s = 0; s < d.slices.size(); s++, g++) {
+          const uint8_t* p; uint32_t len;
+          avr_dbatch_slice(b, g, &p, &len, nullptr);
+          std::vector<uint8_t>& o = decoded[ids[k]][s];
+          o.assign(p, p + len);
+          const Block& blk = d.blocks[d.slice_block[s]];
+          if (blk.has_parity && blk.has_last && blk.last_len > 0) {      // x264 padding patch, recode.cpp:1352-1362, 1387-1391
+            if (blk.parity != (int)(o.size() & 1)) o.push_back(blk.last[0]);
+            else if (!o.empty()) o.back() = blk.last[0];
+          }
+        }
+      }
+    }
+    avr_dbatch_destroy(b);
+  }
+  if (rc != AVR_OK) return rc;
+  for (int f = 0; f < n; f++) {
+    DFile& d = files[f];
+    std::vector<uint8_t> o;
+    o.reserve(d.surrogate.size() + 16);
+    size_t s = 0;
+    std::vector<int> blk_slice(d.blocks.size(), -1);
+    for (size_t k = 0; k < d.slice_block.size(); k++) blk_slice[d.slice_block[k]] = (int)k;
+    for (size_t i = 0; i < d.blocks.size(); i++) {
+      const Block& b = d.blocks[i];
+      if (b.has_literal) o.insert(o.end(), b.literal, b.literal + b.literal_len);
+      else if (b.has_cabac) { const auto& v = decoded[f][blk_slice[i]]; o.insert(o.end(), v.begin(), v.end()); }
+    }
+    (void)s;
+    if (!to_buffer(o, &out[f])) return AVR_E_NOMEM;
+  }
+  if (tacc) *tacc = tt;
+  return AVR_OK;
+}

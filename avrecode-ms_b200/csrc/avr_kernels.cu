@@ -18,7 +18,7 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
   int f = blockIdx.x;
   if (f >= nfiles || threadIdx.x != 0) return;
   const AvrFileDesc fd = fds[f];
-  uint8_t* s0 = store_pool + (size_t)fd.mb_base * 2 * AVR_MB_STRIDE;
+  uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
   uint8_t* s1 = s0 + (size_t)fd.max_mbs * AVR_MB_STRIDE;
   avr_compress_chain_body(fd, bins, blocks, slices, frames, est_pool + (size_t)f * AVR_KEY_COUNT, s0, s1, tab, scratch,
                           scratch_off, scratch_cap, out_len, status);
@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(32) avr_k_decompress_chain(const AvrFileDesc* 
   int f = blockIdx.x;
   if (f >= nfiles || threadIdx.x != 0) return;
   const AvrFileDesc fd = fds[f];
-  uint8_t* s0 = store_pool + (size_t)fd.mb_base * 2 * AVR_MB_STRIDE;
+  uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
   uint8_t* s1 = s0 + (size_t)fd.max_mbs * AVR_MB_STRIDE;
   avr_decompress_chain_body(fd, slices, payloads, est_pool + (size_t)f * AVR_KEY_COUNT, s0, s1, row_pool + fd.mb_base, st, tab,
                             out, out_len, out_bins, status);
@@ -100,5 +100,106 @@ int avr_launch_compact(const uint8_t* scratch, const uint64_t* scratch_off, cons
   avr_k_exclusive_scan_u32<<<1, 1024, 0, st>>>(len, out_off, n, total);
   uint32_t grid = n < 148u * 8u ? n : 148u * 8u;
   avr_k_gather<<<grid, 256, 0, st>>>(scratch, scratch_off, len, out_off, out, n);
+  return (int)cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// Slice-parallel compress pipeline (avr_pipeline.h).  CUB's device radix sort and scans are the
+// plumbing between the hand-written passes.
+#include <cub/cub.cuh>
+
+static AvrPipe make_pipe(const AvrDevBatch& b) {
+  AvrPipe a;
+  a.fds = b.fds; a.bslices = b.bslices; a.nslices = b.nslices; a.blocks = b.blocks; a.nblocks = b.nblocks;
+  a.bins = b.bins; a.frames = b.frames; a.store = b.pic_store; a.seg = b.seg; a.keys = b.keys_a; a.nemit = b.emit_cap;
+  a.prob = b.prob; a.tab = b.tab; a.scratch = b.scratch; a.scratch_off = b.scratch_off; a.scratch_cap = b.scratch_cap;
+  a.out_len = b.out_len; a.status = b.status;
+  return a;
+}
+
+__global__ void __launch_bounds__(256) avr_k_count(AvrPipe a, uint32_t nent) {
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < nent) avr_body_count(a, e);
+  else if (e == nent) a.seg[e] = 0;
+}
+__global__ void __launch_bounds__(256) avr_k_keys(AvrPipe a, uint32_t nent, uint32_t* idx) {
+  uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < nent) avr_body_keys(a, e);
+}
+__global__ void __launch_bounds__(256) avr_k_iota(uint32_t* idx, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) idx[i] = i;
+}
+struct AvrSymBit {
+  const uint32_t* k;
+  __host__ __device__ uint32_t operator()(uint32_t i) const { return k[i] & 1u; }
+};
+struct AvrHeadPos {
+  const uint32_t* k;
+  __host__ __device__ uint32_t operator()(uint32_t i) const { return (i > 0 && (k[i] >> 1) != (k[i - 1] >> 1)) ? i : 0u; }
+};
+struct AvrFnElem {
+  const uint32_t* k; const uint32_t* head; const uint32_t* P;
+  __host__ __device__ AvrHalfSeg operator()(uint32_t i) const { return avr_fn_element(i, k, head, P); }
+};
+__global__ void __launch_bounds__(256) avr_k_estimate(const uint32_t* sorted, const uint32_t* idx, const uint32_t* head,
+                                                      const uint32_t* P, const AvrHalfSeg* fn, uint16_t* prob, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) avr_body_estimate(i, sorted, idx, head, P, fn, prob);
+}
+__global__ void __launch_bounds__(32) avr_k_code(AvrPipe a) {
+  uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < a.nslices) avr_body_code(a, s);
+}
+
+size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bit) {
+  size_t need = 0, t = 0;
+  cub::DeviceScan::ExclusiveSum(nullptr, t, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)(nentries + 1));
+  need = t > need ? t : need;
+  cub::DeviceRadixSort::SortPairs(nullptr, t, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr,
+                                  (int)nemit, 1, sort_end_bit);
+  need = t > need ? t : need;
+  cub::CountingInputIterator<uint32_t> cnt(0);
+  cub::TransformInputIterator<uint32_t, AvrSymBit, cub::CountingInputIterator<uint32_t>> sym(cnt, AvrSymBit{nullptr});
+  cub::DeviceScan::InclusiveSum(nullptr, t, sym, (uint32_t*)nullptr, (int)nemit);
+  need = t > need ? t : need;
+  cub::TransformInputIterator<uint32_t, AvrHeadPos, cub::CountingInputIterator<uint32_t>> hp(cnt, AvrHeadPos{nullptr});
+  cub::DeviceScan::InclusiveScan(nullptr, t, hp, (uint32_t*)nullptr, AvrMaxOp(), (int)nemit);
+  need = t > need ? t : need;
+  cub::TransformInputIterator<AvrHalfSeg, AvrFnElem, cub::CountingInputIterator<uint32_t>> fe(cnt, AvrFnElem{nullptr, nullptr, nullptr});
+  cub::DeviceScan::InclusiveScan(nullptr, t, fe, (AvrHalfSeg*)nullptr, AvrHalfSegOp(), (int)nemit);
+  need = t > need ? t : need;
+  return need + 256;
+}
+
+int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* launches, cudaEvent_t coder_begin, cudaEvent_t coder_end) {
+  if (b.nslices == 0) return 0;
+  AvrPipe a = make_pipe(b);
+  const uint32_t nent = b.nblocks + b.nslices, n = b.emit_cap;
+  size_t tmp = b.cub_tmp_bytes;
+  int nl = 0;
+  AVR_CK(cudaMemsetAsync(b.pic_store, 0, b.pic_store_bytes, st));
+  avr_k_count<<<(nent + 1 + 255) / 256, 256, 0, st>>>(a, nent); nl++;
+  AVR_CK(cub::DeviceScan::ExclusiveSum(b.cub_tmp, tmp, b.seg, b.seg, (int)(nent + 1), st)); nl += 2;
+  avr_k_keys<<<(nent + 255) / 256, 256, 0, st>>>(a, nent, b.idx_a); nl++;
+  avr_k_iota<<<(n + 255) / 256, 256, 0, st>>>(b.idx_a, n); nl++;
+  tmp = b.cub_tmp_bytes;
+  AVR_CK(cub::DeviceRadixSort::SortPairs(b.cub_tmp, tmp, b.keys_a, b.keys_b, b.idx_a, b.idx_b, (int)n, 1, b.sort_end_bit, st));
+  nl += 2 * ((b.sort_end_bit - 1 + 7) / 8) + 1;
+  cub::CountingInputIterator<uint32_t> cnt(0);
+  cub::TransformInputIterator<uint32_t, AvrSymBit, cub::CountingInputIterator<uint32_t>> sym(cnt, AvrSymBit{b.keys_b});
+  tmp = b.cub_tmp_bytes;
+  AVR_CK(cub::DeviceScan::InclusiveSum(b.cub_tmp, tmp, sym, b.psum, (int)n, st)); nl += 2;
+  cub::TransformInputIterator<uint32_t, AvrHeadPos, cub::CountingInputIterator<uint32_t>> hp(cnt, AvrHeadPos{b.keys_b});
+  tmp = b.cub_tmp_bytes;
+  AVR_CK(cub::DeviceScan::InclusiveScan(b.cub_tmp, tmp, hp, b.head, AvrMaxOp(), (int)n, st)); nl += 2;
+  cub::TransformInputIterator<AvrHalfSeg, AvrFnElem, cub::CountingInputIterator<uint32_t>> fe(cnt, AvrFnElem{b.keys_b, b.head, b.psum});
+  tmp = b.cub_tmp_bytes;
+  AVR_CK(cub::DeviceScan::InclusiveScan(b.cub_tmp, tmp, fe, b.fn, AvrHalfSegOp(), (int)n, st)); nl += 2;
+  avr_k_estimate<<<(n + 255) / 256, 256, 0, st>>>(b.keys_b, b.idx_b, b.head, b.psum, b.fn, b.prob, n); nl++;
+  if (coder_begin) cudaEventRecord(coder_begin, st);
+  avr_k_code<<<(b.nslices + 31) / 32, 32, 0, st>>>(a); nl++;
+  if (coder_end) cudaEventRecord(coder_end, st);
+  if (launches) *launches = nl;
   return (int)cudaGetLastError();
 }

@@ -1,0 +1,55 @@
+// Launchers of the sm_100a kernels (avr_kernels.cu).  Raw device pointers and a stream; the
+// host API (avr_api.cu) owns the memory.
+#pragma once
+#include <cuda_runtime.h>
+#include "avr_pipeline.h"
+
+// Device view of a staged compress batch.
+struct AvrDevBatch {
+  int nfiles;
+  uint32_t nslices, nblocks;
+  uint64_t nbins;
+  const AvrFileDesc* fds;
+  const uint16_t* bins;
+  const AvrBlock* blocks;
+  const AvrSlice* slices;          // file-local slice table (chain kernel)
+  const AvrBatchSlice* bslices;    // batch-global slice table (pipeline)
+  const AvrFrame* frames;
+  const AvrTables* tab;
+  // chain kernel state
+  uint16_t* est_pool;              // [nfiles][AVR_KEY_COUNT]
+  uint8_t* store_pool;             // [sum 2*max_mbs][64]
+  // pipeline state
+  uint8_t* pic_store; size_t pic_store_bytes;
+  uint32_t* seg;                   // [nblocks + nslices + 1]
+  uint32_t* keys_a; uint32_t* keys_b; uint32_t* idx_a; uint32_t* idx_b;   // [emit_cap]
+  uint32_t* head; uint32_t* psum; AvrHalfSeg* fn;                         // [emit_cap]
+  uint16_t* prob;                  // [emit_cap]
+  uint32_t emit_cap;               // exact number of coded symbols (host computes it while staging)
+  void* cub_tmp; size_t cub_tmp_bytes;
+  int sort_end_bit;                // 22 + bits(nfiles)
+  // outputs
+  uint8_t* scratch; const uint64_t* scratch_off; const uint32_t* scratch_cap;
+  uint32_t* out_len; int* status;
+  uint64_t* out_off; uint64_t* out_total; uint8_t* out;
+};
+
+struct AvrDevDBatch {
+  int nfiles;
+  uint32_t nslices;
+  const AvrFileDesc* fds;
+  const AvrDecSlice* slices;
+  const uint8_t* payloads;
+  const AvrTables* tab;
+  uint16_t* est_pool;
+  uint8_t* store_pool;
+  avr::MbInfo* row_pool;
+  uint8_t* out; uint32_t* out_len; uint32_t* out_bins; int* status;
+};
+
+int avr_launch_compress_chain(const AvrDevBatch& b, cudaStream_t st);
+int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* launches, cudaEvent_t coder_begin, cudaEvent_t coder_end);
+size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bit);
+int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st);
+int avr_launch_compact(const uint8_t* scratch, const uint64_t* scratch_off, const uint32_t* len, uint64_t* out_off,
+                       uint64_t* total, uint8_t* out, uint32_t n, cudaStream_t st);

@@ -200,18 +200,53 @@ static AVR_HD void avr_body_keys(const AvrPipe& a, uint32_t e) {
   avr_pass_keys_block(blk, stored, seg_end, bins, store, frames, filebits, out);
 }
 
-// After the sort: sorted[i] = (file,key,symbol), idx[i] = emitted index, head[i] = index of the
-// first element of i's key run (max-scan), ones[i] = ones of the run's current period up to and
-// including i (segmented sum), fn[i] = composition of the completed periods of the run up to and
-// including i (segmented monoid scan).  Writes the (symbol, pos, total) record of element i.
-static AVR_HD void avr_body_estimate(uint32_t i, const uint32_t* sorted, const uint32_t* idx, const uint32_t* head,
-                                     const uint32_t* ones, const AvrHalf* fn, uint16_t* prob) {
-  const uint32_t w = sorted[i], sym = w & 1, key = (w >> 1) & 0x1FFFFFu;
-  const uint32_t r = i - head[i];
+// After the sort: sorted[i] = (file,key,symbol), idx[i] = emitted index.  Three plain scans over
+// the sorted array give everything the trajectory needs:
+//   P[i]    inclusive prefix sum of the symbol bit           (ones of ANY range = difference)
+//   head[i] index of the first element of i's key run        (max-scan of head positions)
+//   fn[i]   composition of the halving maps of the run's periods completed up to and
+//           including i                                       (segmented monoid scan)
+static AVR_HD uint32_t avr_ones_between(const uint32_t* P, uint32_t first, uint32_t last_incl) {
+  return P[last_incl] - (first ? P[first - 1] : 0u);
+}
+// element of the fn scan: bit 31 of kflag = starts a key run
+struct AvrHalfSeg { uint32_t a, kflag; };
+static AVR_HD AvrHalfSeg avr_fn_element(uint32_t i, const uint32_t* sorted, const uint32_t* head, const uint32_t* P) {
+  const uint32_t key = (sorted[i] >> 1) & 0x1FFFFFu;
+  const uint32_t h = head[i], r = i - h;
   const AvrPeriod p = avr_period_of(key);
-  const uint32_t ob = avr_is_period_head(r, p) ? 0u : ones[i - 1];
-  uint32_t pos0 = 1;
-  if (r > 0) pos0 = avr_half_apply(fn[i - 1], 1);
+  AvrHalfSeg e;
+  e.a = 0; e.kflag = r == 0 ? 0x80000000u : 0u;
+  if (avr_is_period_tail(r, p)) {
+    const uint32_t first = r + 1 == p.L0 ? h : i + 1 - p.L;     // first element of the period that ends at i
+    e.a = avr_ones_between(P, first, i);
+    e.kflag |= 1;
+  }
+  return e;
+}
+struct AvrHalfSegOp {
+  AVR_HD AvrHalfSeg operator()(const AvrHalfSeg& l, const AvrHalfSeg& r) const {
+    if (r.kflag & 0x80000000u) return r;
+    AvrHalf f = {l.a, l.kflag & 0x7FFFFFFFu}, g = {r.a, r.kflag};
+    AvrHalf h = avr_half_compose(f, g);
+    AvrHalfSeg o = {h.a, h.k | (l.kflag & 0x80000000u)};
+    return o;
+  }
+};
+struct AvrMaxOp { AVR_HD uint32_t operator()(uint32_t a, uint32_t b) const { return a > b ? a : b; } };
+
+static AVR_HD void avr_body_estimate(uint32_t i, const uint32_t* sorted, const uint32_t* idx, const uint32_t* head,
+                                     const uint32_t* P, const AvrHalfSeg* fn, uint16_t* prob) {
+  const uint32_t w = sorted[i], sym = w & 1, key = (w >> 1) & 0x1FFFFFu;
+  const uint32_t h = head[i], r = i - h;
+  const AvrPeriod p = avr_period_of(key);
+  uint32_t ob = 0, pos0 = 1;
+  if (r > 0) {
+    const uint32_t pstart = r < p.L0 ? h : i - (r - p.L0) % p.L;   // first element of i's period
+    if (pstart < i) ob = avr_ones_between(P, pstart, i - 1);
+    AvrHalf f = {fn[i - 1].a, fn[i - 1].kflag & 0x7FFFFFFFu};
+    pos0 = avr_half_apply(f, 1);
+  }
   prob[idx[i]] = avr_prob_pack(sym, pos0 + ob, avr_total_at(r, p));
 }
 

@@ -5,6 +5,7 @@
 // (recode.cpp:1282-1304) of which slices are recoded and which stay literal.
 #include "avr_record.h"
 #include <string.h>
+#include <functional>
 #include "cabac_std.h"
 #include "h264_headers.h"
 
@@ -29,15 +30,11 @@ struct RecordIO {
 
 }  // namespace
 
-int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
-  Recorder rec(out, trace);
+int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice) {
   std::vector<Sps> sps(32);
   std::vector<Pps> pps(256);
   std::vector<uint8_t> rbsp;
   std::vector<uint32_t> map;
-  std::vector<MbInfo> row;
-  uint32_t uid = 0;
-  size_t prev_coded_end = 0;
   size_t pos = 0;
   NalSpan nal;
   while (next_nal(data, n, pos, &nal)) {
@@ -54,40 +51,55 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
     // slice
     int r = 0; { uint8_t v = rbsp[len - 1]; while (!(v & 1)) { v >>= 1; r++; } r++; }  // decode_rbsp_trailing
     const size_t bit_length = 8 * len - (size_t)r;
-    SliceHeaderInfo sh;
-    if (!parse_slice_header(rbsp.data(), bit_length, type, ref_idc, sps.data(), pps.data(), &sh)) continue;
-    if (!sh.cabac) { out->error = AVR_E_UNSUPPORTED; return out->error; }   // CAVLC: nothing to recode
-    if (!sh.supported) { out->error = AVR_E_UNSUPPORTED; return out->error; }
-    if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);  // h264_frame_start
-    const size_t start = (sh.header_bits + 7) / 8;
+    SliceLoc loc;
+    if (!parse_slice_header(rbsp.data(), bit_length, type, ref_idc, sps.data(), pps.data(), &loc.sh)) continue;
+    if (!loc.sh.cabac) return AVR_E_UNSUPPORTED;   // CAVLC: nothing to recode
+    if (!loc.sh.supported) return AVR_E_UNSUPPORTED;
+    const size_t start = (loc.sh.header_bits + 7) / 8;
     if (bit_length <= 8 * start) continue;
-    const size_t size = (bit_length - 8 * start + 7) / 8;
-    const uint8_t* payload = rbsp.data() + start;
-    const size_t raw_off = nal.start + 1 + map[start];
+    loc.size = (bit_length - 8 * start + 7) / 8;
+    loc.payload = rbsp.data() + start;
+    // libavcodec's CABAC reader may look one or two bytes past `size` (a lone 0x80 stop-bit byte
+    // is excluded from size but still in its buffer, cabac_functions.h refill): give ours the same view
+    loc.payload_avail = rbsp.size() - start;
+    loc.raw_off = nal.start + 1 + map[start];
+    int rc = on_slice(loc);
+    if (rc) return rc;
+  }
+  return AVR_OK;
+}
+
+int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
+  Recorder rec(out, trace);
+  std::vector<MbInfo> row;
+  uint32_t uid = 0;
+  size_t prev_coded_end = 0;
+  int rc = scan_annexb_slices(data, n, [&](const SliceLoc& loc) -> int {
+    const SliceHeaderInfo& sh = loc.sh;
+    if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);  // h264_frame_start
     // recode.cpp:1283-1286: memmem of the unescaped payload in the not-yet-emitted original bytes
     bool found = false;
     size_t found_at = 0;
-    if (size >= 8 && raw_off >= prev_coded_end) {
-      size_t hay_end = raw_off + size <= n ? raw_off + size : n;
-      const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, payload, size);
+    if (loc.size >= 8 && loc.raw_off >= prev_coded_end) {
+      size_t hay_end = loc.raw_off + loc.size <= n ? loc.raw_off + loc.size : n;
+      const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, loc.payload, loc.size);
       if (m) { found = true; found_at = (size_t)((const uint8_t*)m - data); }
     }
-    rec.slice_begin(found, found ? found_at : raw_off, (uint32_t)size, sh.sp);
-    if (found) {
-      prev_coded_end = found_at + size;
-      if ((int)row.size() < sh.sp.mb_w) { row.resize((size_t)sh.sp.mb_w); for (auto& m : row) m.uid = 0; }
-      RecordIO io(rec);
-      // libavcodec's CABAC reader may look one or two bytes past `size` (a lone 0x80 stop-bit byte
-      // is excluded from size but still in its buffer, cabac_functions.h refill): give ours the same view
-      io.dec.init(payload, rbsp.size() - start);
-      cabac_init_states(io.st, sh.sp.slice_type == SLICE_I, sh.sp.cabac_init_idc, sh.sp.slice_qp);
-      SliceParser<RecordIO> parser(io, sh.sp, row.data(), ++uid);
-      int rc = parser.run();
-      rec.slice_end();
-      if (rc < 0) { out->error = rc == SYN_E_PCM ? AVR_E_UNSUPPORTED : AVR_E_CORRUPT; return out->error; }
-    }
-  }
-  return AVR_OK;
+    rec.slice_begin(found, found ? found_at : loc.raw_off, (uint32_t)loc.size, sh.sp);
+    if (!found) return 0;
+    prev_coded_end = found_at + loc.size;
+    if ((int)row.size() < sh.sp.mb_w) { row.resize((size_t)sh.sp.mb_w); for (auto& m : row) m.uid = 0; }
+    RecordIO io(rec);
+    io.dec.init(loc.payload, loc.payload_avail);
+    cabac_init_states(io.st, sh.sp.slice_type == SLICE_I, sh.sp.cabac_init_idc, sh.sp.slice_qp);
+    SliceParser<RecordIO> parser(io, sh.sp, row.data(), ++uid);
+    int prc = parser.run();
+    rec.slice_end();
+    if (prc < 0) return prc == SYN_E_PCM ? AVR_E_UNSUPPORTED : AVR_E_CORRUPT;
+    return 0;
+  });
+  out->error = rc;
+  return rc;
 }
 
 }  // namespace avr

@@ -28,6 +28,7 @@ struct FileRecord {
   std::vector<AvrFrame> frames;
   std::vector<SliceSpan> spans;
   uint64_t source_bins = 0;   // get/get_bypass/get_terminate calls on coded slices (SURVEY 8d "bin")
+  uint64_t emitted = 0;       // symbols that go through the range coder: bins minus EOB bins plus nnz side-channel bits
   int out_of_domain = 0;      // bit0: consecutive pictures share frame_num (recode.cpp:831-834 skips bzero)
   int error = 0;              // AVR_E_* from the parse
 };
@@ -95,6 +96,7 @@ class Recorder {
     b.nbins = 0;
     r_->blocks.push_back(b);
     in_sigmap_ = true; expect_eob_ = false;
+    r_->emitted += (uint64_t)avr_nz_bits(max_coeff_);
   }
   void end_sigmap() {
     if (trace_) fprintf(trace_, "]\n");
@@ -115,6 +117,7 @@ class Recorder {
       r_->blocks.back().nbins++;
     }
     r_->bins.push_back(AVR_BIN(sym, ctx, kind));
+    if (kind != AVR_KIND_SIG_EOB) r_->emitted++;
     r_->source_bins++;
   }
 
@@ -126,6 +129,24 @@ class Recorder {
   uint32_t mb_addr_ = 0;
   int cat_ = 0, n_ = 0, max_coeff_ = 0, is_dc_ = 0, c422_ = 0;
 };
+
+}  // namespace avr
+#include <functional>
+#include "h264_headers.h"
+namespace avr {
+
+// One CABAC slice located in an Annex-B stream: what libavcodec knows when it calls
+// CABACCodingHooks::init_decoder (h264_slice.c:2357-2364).
+struct SliceLoc {
+  SliceHeaderInfo sh;
+  size_t raw_off = 0;          // file offset of the first CABAC byte (if the payload has no escapes before it)
+  size_t size = 0;             // CABAC payload bytes libavcodec reports
+  const uint8_t* payload = nullptr;   // unescaped payload (valid during the callback)
+  size_t payload_avail = 0;    // unescaped bytes available from `payload` to the end of the NAL
+};
+// Walks the NALs, tracks SPS/PPS, calls on_slice for every CABAC slice with a non-empty payload.
+// Returns AVR_OK, the callback's non-zero result, or AVR_E_UNSUPPORTED (CAVLC / B / field / FMO / 4:2:2+).
+int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice);
 
 // Native front end: parse an Annex-B H.264 byte stream without libavcodec.
 // Returns AVR_OK, AVR_E_UNSUPPORTED (stream uses syntax outside h264_syntax.h) or AVR_E_CORRUPT.

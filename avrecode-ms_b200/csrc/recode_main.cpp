@@ -1,0 +1,96 @@
+// `recode` CLI, drop-in for the reference's (recode.cpp:1642-1677):
+//   recode compress|decompress|roundtrip <input> [output]      exit 0 / 1
+// plus the batch form the GPU path exists for:
+//   recode compress-batch|roundtrip-batch <file>...            outputs <file>.avrec / report only
+// All entropy coding runs on the GPU through include/avrecode_b200.h; there is no CPU path.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+#include "../../include/avrecode_b200.h"
+
+static bool read_file(const std::string& fn, std::vector<uint8_t>* out) {
+  FILE* f = fopen(fn.c_str(), "rb");
+  if (!f) return false;
+  fseek(f, 0, SEEK_END); long n = ftell(f); fseek(f, 0, SEEK_SET);
+  out->resize((size_t)n);
+  size_t got = n ? fread(out->data(), 1, (size_t)n, f) : 0;
+  fclose(f);
+  return got == (size_t)n;
+}
+static bool write_out(const char* fn, const uint8_t* p, size_t n) {
+  FILE* f = fn ? fopen(fn, "wb") : stdout;
+  if (!f) return false;
+  bool ok = fwrite(p, 1, n, f) == n;
+  if (fn) fclose(f); else fflush(f);
+  return ok;
+}
+static int fail(const std::string& what) {
+  fprintf(stderr, "Exception (avr_error): %s\n", what.c_str());   // shape of recode.cpp:1672-1675
+  return 1;
+}
+static double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) {
+    fprintf(stderr, "Usage: %s [compress|decompress|roundtrip] <input> [output]\n", argv[0]);
+    return 1;
+  }
+  std::string cmd = argv[1];
+  int threads = (int)std::thread::hardware_concurrency();
+  if (threads < 1) threads = 1;
+  bool batch = cmd == "compress-batch" || cmd == "roundtrip-batch";
+  if (!batch && cmd != "compress" && cmd != "decompress" && cmd != "roundtrip") {
+    fprintf(stderr, "Unknown command: %s\n", cmd.c_str());
+    return 1;
+  }
+  std::vector<std::string> names;
+  if (batch) for (int i = 2; i < argc; i++) names.push_back(argv[i]); else names.push_back(argv[2]);
+  const char* outname = (!batch && argc > 3) ? argv[3] : nullptr;
+  std::vector<std::vector<uint8_t>> data(names.size());
+  for (size_t i = 0; i < names.size(); i++)
+    if (!read_file(names[i], &data[i])) return fail("Failed to open file: " + names[i]);
+  avr_context* ctx = nullptr;
+  if (avr_context_create(0, &ctx) != AVR_OK) return fail(avr_last_error());
+  std::vector<const uint8_t*> in; std::vector<size_t> len;
+  for (auto& d : data) { in.push_back(d.data()); len.push_back(d.size()); }
+  const int n = (int)names.size();
+  std::vector<avr_buffer> comp((size_t)n), dec((size_t)n);
+  int rc = 0;
+  if (cmd == "decompress") {
+    if (avr_decompress_files(ctx, in.data(), len.data(), 1, threads, dec.data(), nullptr) != AVR_OK) return fail(avr_last_error());
+    if (!write_out(outname, dec[0].data, dec[0].size)) return fail("write failed");
+    return 0;
+  }
+  avr_timing tc, td;
+  double t0 = now_ms();
+  if (avr_compress_files(ctx, in.data(), len.data(), n, threads, comp.data(), &tc) != AVR_OK) return fail(avr_last_error());
+  double t1 = now_ms();
+  if (cmd == "compress") { if (!write_out(outname, comp[0].data, comp[0].size)) return fail("write failed"); return 0; }
+  if (cmd == "compress-batch") {
+    for (int i = 0; i < n; i++) if (!write_out((names[i] + ".avrec").c_str(), comp[i].data, comp[i].size)) return fail("write failed");
+    return 0;
+  }
+  std::vector<const uint8_t*> cin; std::vector<size_t> clen;
+  for (auto& c : comp) { cin.push_back(c.data); clen.push_back(c.size); }
+  if (avr_decompress_files(ctx, cin.data(), clen.data(), n, threads, dec.data(), &td) != AVR_OK) return fail(avr_last_error());
+  double t2 = now_ms();
+  size_t orig = 0, csz = 0;
+  for (int i = 0; i < n; i++) {
+    orig += data[i].size(); csz += comp[i].size;
+    bool same = dec[i].size == data[i].size() && !memcmp(dec[i].data, data[i].data(), data[i].size());
+    if (!same) { fprintf(stderr, "%s: roundtrip MISMATCH\n", names[i].c_str()); rc = 1; }
+  }
+  // report in the reference's terms (recode.cpp:1618-1635)
+  printf("%s\n", rc ? "Compress-decompress roundtrip failed." : "Compress-decompress roundtrip succeeded:");
+  printf(" compression ratio: %.2f%%\n", orig ? 100.0 * csz / orig : 0.0);
+  printf(" compress: %.1f ms (%.1f MB/s)  decompress: %.1f ms (%.1f MB/s)  bins: %llu\n", t1 - t0, orig / 1e3 / (t1 - t0),
+         t2 - t1, orig / 1e3 / (t2 - t1), (unsigned long long)tc.bins);
+  avr_context_destroy(ctx);
+  return rc;
+}

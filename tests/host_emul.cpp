@@ -107,22 +107,21 @@ static int compress_pipeline(const std::vector<const avr::FileRecord*>& recs, co
   for (uint32_t e = 0; e < nent; e++) avr_body_keys(a, e);
   for (uint32_t i = 0; i < run; i++) idx[i] = i;
   std::stable_sort(idx.begin(), idx.end(), [&](uint32_t x, uint32_t y) { return (keys[x] >> 1) < (keys[y] >> 1); });
-  std::vector<uint32_t> sorted(run), head(run), ones(run);
-  std::vector<AvrHalf> fn(run);
+  std::vector<uint32_t> sorted(run), head(run), P(run);
+  std::vector<AvrHalfSeg> fn(run);
   for (uint32_t i = 0; i < run; i++) sorted[i] = keys[idx[i]];
-  for (uint32_t i = 0; i < run; i++) {
+  for (uint32_t i = 0; i < run; i++) {                       // cub::DeviceScan::InclusiveSum / InclusiveScan(max)
     bool kh = i == 0 || (sorted[i] >> 1) != (sorted[i - 1] >> 1);
     head[i] = kh ? i : head[i - 1];
-    uint32_t r = i - head[i];
-    AvrPeriod p = avr_period_of((sorted[i] >> 1) & 0x1FFFFFu);
-    ones[i] = (avr_is_period_head(r, p) ? 0 : ones[i - 1]) + (sorted[i] & 1);
-    AvrHalf el = {0, 0};
-    if (avr_is_period_tail(r, p)) { el.a = ones[i]; el.k = 1; }
-    fn[i] = kh ? el : avr_half_compose(fn[i - 1], el);
+    P[i] = (i ? P[i - 1] : 0) + (sorted[i] & 1);
+  }
+  for (uint32_t i = 0; i < run; i++) {                       // cub::DeviceScan::InclusiveScan(AvrHalfSegOp)
+    AvrHalfSeg el = avr_fn_element(i, sorted.data(), head.data(), P.data());
+    fn[i] = i ? AvrHalfSegOp()(fn[i - 1], el) : el;
   }
   std::vector<uint16_t> prob(run);
   a.prob = prob.data();
-  for (uint32_t i = 0; i < run; i++) avr_body_estimate(i, sorted.data(), idx.data(), head.data(), ones.data(), fn.data(), prob.data());
+  for (uint32_t i = 0; i < run; i++) avr_body_estimate(i, sorted.data(), idx.data(), head.data(), P.data(), fn.data(), prob.data());
   std::vector<uint64_t> soff(a.nslices); std::vector<uint32_t> scap(a.nslices), olen(a.nslices);
   std::vector<int> status(a.nslices);
   uint64_t total = 0;
