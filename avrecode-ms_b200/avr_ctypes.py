@@ -1,0 +1,240 @@
+"""ctypes binding of the C ABI (include/avrecode_b200.h) for tests/ and bench.py.
+
+This is the same stub a maintainer of the reference would write for any FFI (INTEGRATION.md shows
+the C++ one); it adds no logic.  Every compute call goes to libavrecode_b200.so -> CUDA; if the
+library is missing or no sm_100 GPU is usable the calls raise, there is no fallback.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libavrecode_b200.so")
+
+AVR_OK = 0
+MODE_PIPELINE = 0
+MODE_CHAIN = 1
+
+EXPORTS = [
+    "avr_version", "avr_last_error", "avr_context_create", "avr_context_destroy", "avr_context_stream",
+    "avr_record_new", "avr_record_free", "avr_rec_frame_spec", "avr_rec_slice_begin", "avr_rec_slice_end",
+    "avr_rec_mb_xy", "avr_rec_begin_sub_mb", "avr_rec_end_sub_mb", "avr_rec_begin_coding_type",
+    "avr_rec_end_coding_type", "avr_rec_bin", "avr_record_annexb", "avr_record_counts", "avr_record_span",
+    "avr_cbatch_create", "avr_cbatch_run", "avr_cbatch_fetch", "avr_cbatch_payload", "avr_cbatch_timing",
+    "avr_cbatch_destroy", "avr_dbatch_create", "avr_dbatch_run", "avr_dbatch_fetch", "avr_dbatch_slice",
+    "avr_dbatch_timing", "avr_dbatch_destroy", "avr_compress_files", "avr_decompress_files", "avr_buffer_free",
+]
+
+
+class SliceParams(C.Structure):
+    _fields_ = [("slice_type", C.c_int32), ("first_mb", C.c_int32), ("mb_w", C.c_int32), ("mb_h", C.c_int32),
+                ("num_ref", C.c_int32 * 2), ("cabac_init_idc", C.c_int32), ("slice_qp", C.c_int32),
+                ("transform_8x8_mode", C.c_int32), ("chroma_format_idc", C.c_int32),
+                ("direct_8x8_inference", C.c_int32)]
+
+
+class DSlice(C.Structure):
+    _fields_ = [("payload", C.c_void_p), ("payload_len", C.c_uint32), ("size", C.c_uint32), ("flip", C.c_uint32),
+                ("sp", SliceParams)]
+
+
+class Timing(C.Structure):
+    _fields_ = [("h2d_ms", C.c_double), ("kernel_ms", C.c_double), ("d2h_ms", C.c_double),
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("bins", C.c_uint64),
+                ("coded_symbols", C.c_uint64), ("launches", C.c_uint32), ("coder_launch_ms_x1000", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class Buffer(C.Structure):
+    _fields_ = [("data", C.POINTER(C.c_uint8)), ("size", C.c_size_t)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = C.CDLL(LIB_PATH)
+        L.avr_last_error.restype = C.c_char_p
+        L.avr_context_stream.restype = C.c_void_p
+        L.avr_record_new.restype = C.c_void_p
+        for name in EXPORTS:
+            getattr(L, name)  # AttributeError if the ABI lost a symbol
+        L.avr_context_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.avr_context_destroy.argtypes = [C.c_void_p]
+        L.avr_context_stream.argtypes = [C.c_void_p]
+        L.avr_record_free.argtypes = [C.c_void_p]
+        L.avr_record_annexb.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t]
+        L.avr_record_counts.argtypes = [C.c_void_p, C.POINTER(C.c_uint64)]
+        L.avr_record_span.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32),
+                                      C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(SliceParams)]
+        L.avr_cbatch_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p)]
+        L.avr_cbatch_run.argtypes = [C.c_void_p, C.c_int]
+        L.avr_cbatch_fetch.argtypes = [C.c_void_p]
+        L.avr_cbatch_payload.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.POINTER(C.POINTER(C.c_uint8)),
+                                         C.POINTER(C.c_uint32)]
+        L.avr_cbatch_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+        L.avr_cbatch_destroy.argtypes = [C.c_void_p]
+        L.avr_dbatch_create.argtypes = [C.c_void_p, C.POINTER(DSlice), C.POINTER(C.c_uint32), C.c_int,
+                                        C.POINTER(C.c_void_p)]
+        L.avr_dbatch_run.argtypes = [C.c_void_p]
+        L.avr_dbatch_fetch.argtypes = [C.c_void_p]
+        L.avr_dbatch_slice.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(C.c_uint32),
+                                       C.POINTER(C.c_uint32)]
+        L.avr_dbatch_timing.argtypes = [C.c_void_p, C.POINTER(Timing)]
+        L.avr_dbatch_destroy.argtypes = [C.c_void_p]
+        L.avr_compress_files.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_int, C.c_int,
+                                         C.POINTER(Buffer), C.POINTER(Timing)]
+        L.avr_decompress_files.argtypes = L.avr_compress_files.argtypes
+        L.avr_buffer_free.argtypes = [C.POINTER(Buffer)]
+        _lib = L
+    return _lib
+
+
+class AvrError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != AVR_OK:
+        raise AvrError(f"avr error {rc}: {lib().avr_last_error().decode()}")
+
+
+class Context:
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        _check(lib().avr_context_create(device, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().avr_context_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+class Record:
+    """Host records of one file (native Annex-B front end)."""
+
+    def __init__(self, data: bytes):
+        self.h = C.c_void_p(lib().avr_record_new())
+        self.rc = lib().avr_record_annexb(self.h, data, len(data))
+        c = (C.c_uint64 * 6)()
+        lib().avr_record_counts(self.h, c)
+        self.bins, self.blocks, self.slices, self.nspans, self.pictures, self.out_of_domain = [int(x) for x in c]
+
+    def spans(self):
+        out = []
+        for i in range(self.nspans):
+            off, size, idx, flip, sp = C.c_uint64(), C.c_uint32(), C.c_int32(), C.c_uint32(), SliceParams()
+            _check(lib().avr_record_span(self.h, i, C.byref(off), C.byref(size), C.byref(idx), C.byref(flip), C.byref(sp)))
+            out.append(dict(payload_off=off.value, size=size.value, slice_index=idx.value, flip=flip.value, sp=sp))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().avr_record_free(self.h)
+            self.h = C.c_void_p()
+
+
+class CBatch:
+    def __init__(self, ctx: Context, records):
+        self.records = records
+        arr = (C.c_void_p * len(records))(*[r.h for r in records])
+        self.h = C.c_void_p()
+        _check(lib().avr_cbatch_create(ctx.h, arr, len(records), C.byref(self.h)))
+
+    def run(self, mode=MODE_PIPELINE):
+        _check(lib().avr_cbatch_run(self.h, mode))
+
+    def fetch(self):
+        _check(lib().avr_cbatch_fetch(self.h))
+
+    def payload(self, file, slice_):
+        p, n = C.POINTER(C.c_uint8)(), C.c_uint32()
+        _check(lib().avr_cbatch_payload(self.h, file, slice_, C.byref(p), C.byref(n)))
+        return C.string_at(p, n.value)
+
+    def payloads(self):
+        return [[self.payload(f, s) for s in range(r.slices)] for f, r in enumerate(self.records)]
+
+    def timing(self):
+        t = Timing()
+        lib().avr_cbatch_timing(self.h, C.byref(t))
+        return t.as_dict()
+
+    def close(self):
+        if self.h:
+            lib().avr_cbatch_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class DBatch:
+    """slices_per_file: list (per file) of dicts(payload=bytes, size, flip, sp=SliceParams)."""
+
+    def __init__(self, ctx: Context, slices_per_file):
+        flat = [s for f in slices_per_file for s in f]
+        self._keep = [C.create_string_buffer(s["payload"], len(s["payload"])) for s in flat]
+        arr = (DSlice * max(1, len(flat)))()
+        for i, s in enumerate(flat):
+            arr[i].payload = C.cast(self._keep[i], C.c_void_p)
+            arr[i].payload_len = len(s["payload"])
+            arr[i].size = s["size"]
+            arr[i].flip = s["flip"]
+            arr[i].sp = s["sp"]
+        per = (C.c_uint32 * max(1, len(slices_per_file)))(*[len(f) for f in slices_per_file])
+        self.n = len(flat)
+        self.h = C.c_void_p()
+        _check(lib().avr_dbatch_create(ctx.h, arr, per, len(slices_per_file), C.byref(self.h)))
+
+    def run(self):
+        _check(lib().avr_dbatch_run(self.h))
+
+    def fetch(self):
+        _check(lib().avr_dbatch_fetch(self.h))
+
+    def slice(self, i):
+        p, n, b = C.POINTER(C.c_uint8)(), C.c_uint32(), C.c_uint32()
+        _check(lib().avr_dbatch_slice(self.h, i, C.byref(p), C.byref(n), C.byref(b)))
+        return C.string_at(p, n.value), b.value
+
+    def timing(self):
+        t = Timing()
+        lib().avr_dbatch_timing(self.h, C.byref(t))
+        return t.as_dict()
+
+    def close(self):
+        if self.h:
+            lib().avr_dbatch_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+def _files_call(fn, ctx, blobs, threads):
+    n = len(blobs)
+    ins = (C.c_char_p * n)(*blobs)
+    lens = (C.c_size_t * n)(*[len(b) for b in blobs])
+    outs = (Buffer * n)()
+    t = Timing()
+    _check(fn(ctx.h, ins, lens, n, threads, outs, C.byref(t)))
+    res = [C.string_at(outs[i].data, outs[i].size) for i in range(n)]
+    for i in range(n):
+        lib().avr_buffer_free(C.byref(outs[i]))
+    return res, t.as_dict()
+
+
+def compress_files(ctx, blobs, threads=0):
+    """`recode compress` for a batch of Annex-B H.264 byte strings -> .avrec byte strings."""
+    return _files_call(lib().avr_compress_files, ctx, blobs, threads or (os.cpu_count() or 1))
+
+
+def decompress_files(ctx, blobs, threads=0):
+    """`recode decompress` for a batch of .avrec byte strings -> original byte strings."""
+    return _files_call(lib().avr_decompress_files, ctx, blobs, threads or (os.cpu_count() or 1))

@@ -495,6 +495,9 @@ static bool decode_trace(const Trace& tr, const std::vector<std::vector<uint8_t>
       case '[':
         if (!coded) break;
         m.begin_sigmap();
+        // the compressor updates is_8x8 (end_coding_type, :951) BEFORE it codes the nnz bits
+        // (:1215-1219); the reference decompressor reads it before (:1485-1487) -- its 8x8 bug
+        if (!ref_quirks && m.size > 32) m.frames[m.cur].at(m.mb_x, m.mb_y).is_8x8 = 1;
         m.nz_side_channel([&](std::tuple<int, int, int> k, int* bit) {
           *bit = dec->get(Model::p1(m.E(k), dec->range));
           m.update(*bit, k);

@@ -1,0 +1,74 @@
+import os
+import subprocess
+import sys
+import tempfile
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "avrecode-ms_b200")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, PKG)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+REF = os.path.join(ROOT, "oracle", "_ref")
+GOLDEN_NAMES = ["ip_basic", "multislice_multiref", "dct8x8", "dense_full_blocks", "skippy_idr"]
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def built():
+    need = [os.path.join(PKG, "libavrecode_b200.so"), os.path.join(PKG, "bin", "avrgen"),
+            os.path.join(ROOT, "build", "avr_emul"), os.path.join(REF, "avr_oracle")]
+    if not all(os.path.exists(p) for p in need):
+        import __graft_entry__ as g
+        g.build()
+    return True
+
+
+def have_ref():
+    return os.path.exists(os.path.join(REF, "recode")) and os.path.exists(os.path.join(REF, "ref_harness"))
+
+
+def run(cmd, **kw):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, **kw)
+    return r.returncode, r.stdout, r.stderr
+
+
+def gen_clip(path, **params):
+    args = [os.path.join(PKG, "bin", "avrgen"), path] + [f"{k}={v}" for k, v in params.items()]
+    rc, _, err = run(args)
+    assert rc == 0, err
+    return open(path, "rb").read()
+
+
+def ref_trace(clip_path, out_path):
+    with open(out_path, "wb") as f:
+        subprocess.run([os.path.join(REF, "ref_harness"), "trace", clip_path], stdout=f, stderr=subprocess.DEVNULL, check=True)
+
+
+def oracle_encode(trace_path):
+    rc, out, err = run([os.path.join(REF, "avr_oracle"), "encode", trace_path])
+    assert rc == 0, err
+    return [bytes.fromhex(l[2:].decode()) for l in out.splitlines() if l.startswith(b"P ")]
+
+
+def hex_payloads(out):
+    return [bytes.fromhex(l[2:].decode()) for l in out.splitlines() if l.startswith(b"P ")]
+
+
+def golden_trace(name, td):
+    import gzip
+    p = os.path.join(td, name + ".trace")
+    with open(p, "wb") as f:
+        f.write(gzip.open(os.path.join(GOLDEN, name + ".trace.gz")).read())
+    return p
+
+
+@pytest.fixture
+def tmpdir_path():
+    with tempfile.TemporaryDirectory() as td:
+        yield td

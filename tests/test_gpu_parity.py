@@ -1,0 +1,125 @@
+"""Parity tests proper: the CUDA path through the C ABI against the oracle, the golden reference
+containers, and size-independent properties (roundtrip == input)."""
+import os
+
+import pytest
+
+from avrec_wire import parse_avrec
+from conftest import GOLDEN, GOLDEN_NAMES, REF, gen_clip, have_ref, oracle_encode, ref_trace, run, golden_trace
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import avr_ctypes as A
+    c = A.Context(0)
+    yield c
+    c.close()
+
+
+def golden_payloads(name):
+    return [b["cabac"] for b in parse_avrec(open(os.path.join(GOLDEN, name + ".avrec"), "rb").read()) if "cabac" in b]
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_payloads_match_reference_golden(ctx, name, mode):
+    import avr_ctypes as A
+    rec = A.Record(open(os.path.join(GOLDEN, name + ".h264"), "rb").read())
+    assert rec.rc == 0
+    b = A.CBatch(ctx, [rec])
+    b.run(mode)
+    b.fetch()
+    assert b.payloads()[0] == golden_payloads(name)
+    b.close()
+    rec.close()
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_container_is_byte_identical_to_reference(ctx, name):
+    """.avrec bytes == the unmodified reference's `recode compress` output (golden)."""
+    import avr_ctypes as A
+    data = open(os.path.join(GOLDEN, name + ".h264"), "rb").read()
+    comp, _ = A.compress_files(ctx, [data])
+    assert comp[0] == open(os.path.join(GOLDEN, name + ".avrec"), "rb").read()
+
+
+def test_decompress_reference_containers(ctx):
+    """our decompressor restores the input from containers written by the REFERENCE compressor"""
+    import avr_ctypes as A
+    blobs = [open(os.path.join(GOLDEN, n + ".avrec"), "rb").read() for n in GOLDEN_NAMES]
+    out, t = A.decompress_files(ctx, blobs)
+    for n, o in zip(GOLDEN_NAMES, out):
+        assert o == open(os.path.join(GOLDEN, n + ".h264"), "rb").read(), n
+    assert t["bins"] > 0
+
+
+def test_batch_pipeline_equals_chain_and_oracle(ctx, tmpdir_path):
+    import avr_ctypes as A
+    params = [dict(seed=40 + i, mb_w=8 + 3 * i, mb_h=6 + i, frames=3 + i, slices_per_frame=1 + i % 3,
+                   transform_8x8=i % 2, num_ref=1 + i % 3) for i in range(6)]
+    datas, wants = [], []
+    for i, p in enumerate(params):
+        clip = os.path.join(tmpdir_path, f"c{i}.h264")
+        datas.append(gen_clip(clip, **p))
+        if have_ref():
+            tr = os.path.join(tmpdir_path, f"c{i}.trace")
+            ref_trace(clip, tr)
+            wants.append(oracle_encode(tr))
+    recs = [A.Record(d) for d in datas]
+    res = []
+    for mode in (A.MODE_PIPELINE, A.MODE_CHAIN):
+        b = A.CBatch(ctx, recs)
+        b.run(mode)
+        b.fetch()
+        res.append(b.payloads())
+        b.close()
+    assert res[0] == res[1]
+    if wants:
+        assert res[0] == wants
+    comp, _ = A.compress_files(ctx, datas)
+    back, _ = A.decompress_files(ctx, comp)
+    assert back == datas
+
+
+def test_edge_inputs(ctx, tmpdir_path):
+    """empty file, junk, a stream with no slices, slices too short to recode (< 8 bytes -> skip_coded)"""
+    import avr_ctypes as A
+    clip = gen_clip(os.path.join(tmpdir_path, "s.h264"), seed=50, mb_w=2, mb_h=1, frames=6, p_skip=250)
+    sps_pps_only = clip[:clip.find(b"\x00\x00\x01\x65") if b"\x00\x00\x01\x65" in clip else 40]
+    blobs = [b"", b"junk that is not h264" * 10, sps_pps_only, clip]
+    comp, _ = A.compress_files(ctx, blobs)
+    back, _ = A.decompress_files(ctx, comp)
+    assert back == blobs
+    kinds = [k for b in parse_avrec(comp[3]) for k in b if k in ("skip_coded", "cabac")]
+    assert "skip_coded" in kinds or "cabac" in kinds
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+def test_container_identical_to_live_reference_with_skipped_slices(ctx, tmpdir_path):
+    import avr_ctypes as A
+    clip = os.path.join(tmpdir_path, "c.h264")
+    data = gen_clip(clip, seed=51, mb_w=4, mb_h=3, frames=10, p_skip=235, slices_per_frame=2)
+    avrec = os.path.join(tmpdir_path, "c.avrec")
+    rc, _, err = run([os.path.join(REF, "recode"), "compress", clip, avrec])
+    assert rc == 0, err
+    comp, _ = A.compress_files(ctx, [data])
+    assert comp[0] == open(avrec, "rb").read()
+
+
+def test_large_roundtrip_property(ctx, tmpdir_path):
+    """bench-sized property check: decompress(compress(x)) == x on a 1080p multi-slice clip, and
+    pipeline == chain on the same records"""
+    import avr_ctypes as A
+    data = gen_clip(os.path.join(tmpdir_path, "big.h264"), seed=60, mb_w=120, mb_h=68, frames=6, slices_per_frame=8,
+                    transform_8x8=1, num_ref=2)
+    comp, tc = A.compress_files(ctx, [data])
+    back, td = A.decompress_files(ctx, comp)
+    assert back[0] == data
+    assert tc["bins"] == td["bins"] > 1_000_000
+    rec = A.Record(data)
+    res = []
+    for mode in (0, 1):
+        b = A.CBatch(ctx, [rec]); b.run(mode); b.fetch(); res.append(b.payloads()); b.close()
+    assert res[0] == res[1]

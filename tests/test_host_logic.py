@@ -1,0 +1,58 @@
+"""Device logic on the CPU: tests/host_emul.cpp compiles the kernel bodies for the host and runs
+them as an emulated grid (test scaffold, not a product path).  Checks them against the golden
+reference containers and the oracle."""
+import os
+
+import pytest
+
+from avrec_wire import parse_avrec
+from conftest import GOLDEN, GOLDEN_NAMES, ROOT, gen_clip, have_ref, hex_payloads, oracle_encode, ref_trace, run
+
+EMUL = os.path.join(ROOT, "build", "avr_emul")
+
+
+def golden_payloads(name):
+    return [b["cabac"] for b in parse_avrec(open(os.path.join(GOLDEN, name + ".avrec"), "rb").read()) if "cabac" in b]
+
+
+@pytest.mark.parametrize("mode", ["chain", "pipeline"])
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_compress_bodies_match_reference_golden(name, mode):
+    rc, out, err = run([EMUL, mode, os.path.join(GOLDEN, name + ".h264")])
+    assert rc == 0, err
+    assert hex_payloads(out) == golden_payloads(name)
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_decompress_body_restores_original_cabac_bytes(name):
+    rc, out, err = run([EMUL, "roundtrip", os.path.join(GOLDEN, name + ".h264")])
+    assert rc == 0 and out.startswith(b"OK"), out + err
+
+
+def test_pipeline_batch_of_files_keeps_models_separate():
+    """the estimator state is per file (recode.cpp:1314): other files in the batch must not leak in"""
+    clips = [os.path.join(GOLDEN, n + ".h264") for n in ("dct8x8", "skippy_idr", "ip_basic")]
+    rc, out, err = run([EMUL, "pipeline"] + clips)
+    assert rc == 0, err
+    assert hex_payloads(out) == golden_payloads("dct8x8")
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("params", [
+    dict(seed=31, mb_w=20, mb_h=12, frames=5, slices_per_frame=4, p_skip=200),     # lone 0x80 stop-bit bytes
+    dict(seed=32, mb_w=16, mb_h=9, frames=12, transform_8x8=1, num_ref=4),          # > 95 symbols on many keys
+    dict(seed=33, mb_w=11, mb_h=7, frames=6, idr_period=2, qp=12, cabac_init_idc=1),
+    dict(seed=34, mb_w=7, mb_h=5, frames=3, p_sig=252, p_last=1, p_cbf=254, p_cbp=254, transform_8x8=1),  # full blocks
+])
+def test_bodies_match_oracle_on_fresh_clips(params, tmpdir_path):
+    clip = os.path.join(tmpdir_path, "c.h264")
+    gen_clip(clip, **params)
+    tr = os.path.join(tmpdir_path, "c.trace")
+    ref_trace(clip, tr)
+    want = oracle_encode(tr)
+    for mode in ("chain", "pipeline"):
+        rc, out, err = run([EMUL, mode, clip])
+        assert rc == 0, err
+        assert hex_payloads(out) == want, mode
+    rc, out, err = run([EMUL, "roundtrip", clip])
+    assert rc == 0 and out.startswith(b"OK"), out + err
