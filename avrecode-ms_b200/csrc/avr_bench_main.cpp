@@ -1,0 +1,94 @@
+// avrbench: native timing / profiling harness over the C ABI (no Python in the process, so it can
+// run under ncu and compute-sanitizer).
+//   avrbench <reps> <mode: 0 pipeline | 1 chain | 2 decompress only> <clip.h264>...
+// Stages the clips' records once, runs compress `reps` times, stages the payloads, runs
+// decompress `reps` times, verifies the re-encoded CABAC bytes against the input files and
+// prints one line of JSON with the CUDA-event times.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/avrecode_b200.h"
+
+static bool read_file(const char* fn, std::vector<uint8_t>* out) {
+  FILE* f = fopen(fn, "rb");
+  if (!f) return false;
+  fseek(f, 0, SEEK_END); long n = ftell(f); fseek(f, 0, SEEK_SET);
+  out->resize((size_t)n);
+  size_t got = n ? fread(out->data(), 1, (size_t)n, f) : 0;
+  fclose(f);
+  return got == (size_t)n;
+}
+#define CHECK(x) do { int rc_ = (x); if (rc_ != AVR_OK) { fprintf(stderr, "%s -> %d: %s\n", #x, rc_, avr_last_error()); return 1; } } while (0)
+
+int main(int argc, char** argv) {
+  if (argc < 4) { fprintf(stderr, "usage: %s <reps> <mode> <clip>...\n", argv[0]); return 2; }
+  const int reps = atoi(argv[1]), mode = atoi(argv[2]);
+  const int n = argc - 3;
+  std::vector<std::vector<uint8_t>> data((size_t)n);
+  std::vector<avr_record*> recs((size_t)n);
+  uint64_t bins = 0, bytes = 0;
+  for (int i = 0; i < n; i++) {
+    if (!read_file(argv[3 + i], &data[i])) { fprintf(stderr, "cannot read %s\n", argv[3 + i]); return 2; }
+    recs[i] = avr_record_new();
+    CHECK(avr_record_annexb(recs[i], data[i].data(), data[i].size()));
+    uint64_t c[6]; avr_record_counts(recs[i], c);
+    bins += c[0]; bytes += data[i].size();
+  }
+  avr_context* ctx;
+  CHECK(avr_context_create(0, &ctx));
+  avr_cbatch* cb;
+  CHECK(avr_cbatch_create(ctx, recs.data(), n, &cb));
+  avr_timing tc; memset(&tc, 0, sizeof tc);
+  double c_ms = 0, coder_ms = 0;
+  const int cmode = mode == 1 ? AVR_MODE_CHAIN : AVR_MODE_PIPELINE;
+  const int creps = mode == 2 ? 1 : reps;
+  for (int r = 0; r < creps; r++) {
+    CHECK(avr_cbatch_run(cb, cmode));
+    avr_cbatch_timing(cb, &tc);
+    c_ms += tc.kernel_ms; coder_ms += tc.coder_launch_ms_x1000 / 1000.0;
+  }
+  CHECK(avr_cbatch_fetch(cb));
+  // decompress batch from the payloads
+  std::vector<avr_dslice> sl; std::vector<uint32_t> per((size_t)n, 0);
+  std::vector<std::pair<int, uint64_t>> where;   // (file, payload_off) per coded slice
+  for (int i = 0; i < n; i++) {
+    uint64_t c[6]; avr_record_counts(recs[i], c);
+    for (uint32_t k = 0; k < c[3]; k++) {
+      uint64_t off; uint32_t size, flip; int32_t idx; avr_slice_params sp;
+      avr_record_span(recs[i], k, &off, &size, &idx, &flip, &sp);
+      if (idx < 0) continue;
+      avr_dslice d; memset(&d, 0, sizeof d);
+      avr_cbatch_payload(cb, i, (uint32_t)idx, &d.payload, &d.payload_len);
+      d.size = size; d.flip = flip; d.sp = sp;
+      sl.push_back(d); per[i]++; where.push_back({i, off});
+    }
+  }
+  avr_dbatch* db;
+  CHECK(avr_dbatch_create(ctx, sl.data(), per.data(), n, &db));
+  avr_timing td; memset(&td, 0, sizeof td);
+  double d_ms = 0;
+  const int dreps = mode == 1 ? 1 : reps;
+  for (int r = 0; r < dreps; r++) {
+    CHECK(avr_dbatch_run(db));
+    avr_dbatch_timing(db, &td);
+    d_ms += td.kernel_ms;
+  }
+  CHECK(avr_dbatch_fetch(db));
+  int bad = 0;
+  for (size_t s = 0; s < sl.size(); s++) {
+    const uint8_t* p; uint32_t len, b;
+    avr_dbatch_slice(db, (uint32_t)s, &p, &len, &b);
+    const uint8_t* orig = data[where[s].first].data() + where[s].second;
+    // all bytes but the last (recode.cpp:1352-1362 patches it) must match
+    uint32_t cmp = len < sl[s].size ? len : sl[s].size;
+    if (len + 1 < sl[s].size || len > sl[s].size || (cmp > 1 && memcmp(p, orig, cmp - 1))) bad++;
+  }
+  printf("{\"files\": %d, \"bins\": %llu, \"bytes\": %llu, \"slices\": %zu, \"compress_ms\": %.3f, \"coder_ms\": %.3f, "
+         "\"decompress_ms\": %.3f, \"compress_mbins_s\": %.1f, \"decompress_mbins_s\": %.1f, \"bad_slices\": %d}\n",
+         n, (unsigned long long)bins, (unsigned long long)bytes, sl.size(), c_ms / creps, coder_ms / creps, d_ms / dreps,
+         bins / 1e3 / (c_ms / creps), bins / 1e3 / (d_ms / dreps), bad);
+  avr_dbatch_destroy(db); avr_cbatch_destroy(cb); avr_context_destroy(ctx);
+  return bad ? 1 : 0;
+}

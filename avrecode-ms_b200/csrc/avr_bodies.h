@@ -7,10 +7,14 @@
 #include "h264_std_tables.h"
 
 // Constant tables every kernel needs, uploaded once per context (avr_api.cu).
-struct AvrTables {
+struct AvrHotTabs {            // the per-bin tables: copied to shared memory by the chain kernels
   AvrDivTab div;
   uint8_t range_lps[256];     // ITU-T H.264 Table 9-44, [pStateIdx*4 + qCodIRangeIdx]
   uint8_t trans_lps[64];      // Table 9-45
+  uint8_t pad[6];
+};
+struct AvrTables {
+  AvrHotTabs hot;
   int8_t ctx_m[4][1024];      // Tables 9-12..9-33: plane 0 = I, 1..3 = cabac_init_idc 0..2
   int8_t ctx_n[4][1024];
 };
@@ -57,7 +61,7 @@ static AVR_HDN void avr_compress_chain_body(const AvrFileDesc& fd, const uint16_
   const AvrBlock* blocks = blocks_all + fd.block_off;
   const AvrFrame* frames = frames_all + fd.frame_off;
   AvrChain ch;
-  ch.init(est, store0, store1, fd.max_mbs, &tab->div);
+  ch.init(est, store0, store1, fd.max_mbs, &tab->hot.div);
   int curf = -1;
   for (uint32_t s = 0; s < fd.nslices; s++) {
     const AvrSlice sl = slices_all[fd.slice_off + s];
@@ -131,7 +135,7 @@ struct AvrDecodeIO {
   AvrRangeDec dec;
   AvrCabacEnc cab;
   uint8_t* st;                  // [1024] CABAC context states of this slice
-  const AvrTables* tab;
+  const AvrHotTabs* hot;
   uint32_t mb_addr;
   int cat, n, size, is_dc, c422;
   int in_sigmap, expect_eob, zz, observed, stored, ones, ended_by_eob;
@@ -154,7 +158,7 @@ struct AvrDecodeIO {
     } else {
       sym = ch->decode(dec, (uint32_t)ctx, 0x60);
     }
-    cab.put(sym, &st[ctx], tab->range_lps, tab->trans_lps);
+    cab.put(sym, &st[ctx], hot->range_lps, hot->trans_lps);
     return sym;
   }
   AVR_HD int bypass(int) {
@@ -196,43 +200,59 @@ struct AvrDecodeIO {
 };
 
 // CABAC context initialisation (ITU-T H.264 9.3.1.1; reference ffmpeg h264_cabac.c:1267-1286).
-static AVR_HDN void avr_cabac_init_states(uint8_t* st, const AvrTables* tab, int is_intra, int init_idc, int qp) {
+static AVR_HDN void avr_cabac_init_states(uint8_t* st, const AvrTables* tab, int is_intra, int init_idc, int qp,
+                                          int lane, int nlanes) {
   const int pl = is_intra ? 0 : 1 + init_idc;
   qp = qp < 0 ? 0 : qp > 51 ? 51 : qp;
-  for (int i = 0; i < 1024; i++) {
+  for (int i = lane; i < 1024; i += nlanes) {
     int pre = ((tab->ctx_m[pl][i] * qp) >> 4) + tab->ctx_n[pl][i];
     pre = pre < 1 ? 1 : pre > 126 ? 126 : pre;
     st[i] = pre <= 63 ? (uint8_t)((63 - pre) << 1) : (uint8_t)(((pre - 64) << 1) | 1);
   }
 }
 
+// Per-file decompress state that survives from slice to slice (lives in lane 0's registers /
+// the block's shared memory in the kernel).
+struct AvrDecState {
+  AvrChain ch;
+  uint32_t uid;
+  int failed;
+};
+
+// One coded slice, executed by ONE thread (the chain).  st[] must already hold the slice's initial
+// CABAC states and the picture stores must already be flipped (both done cooperatively by the
+// caller: avr_k_decompress_chain / the host emulation).
+static AVR_HDN void avr_decompress_slice(AvrDecState& S, const AvrDecSlice& ds, const uint8_t* payloads, avr::MbInfo* row,
+                                         uint8_t* st, const AvrHotTabs* hot, uint8_t* out, uint32_t* out_len,
+                                         uint32_t* out_bins, int* status) {
+  if (S.failed) { *out_len = 0; *out_bins = 0; *status = AVR_E_CORRUPT; return; }   // model state is meaningless after a failed slice
+  if (S.uid == 0) for (int x = 0; x < ds.sp.mb_w; x++) row[x].uid = 0;
+  AvrDecodeIO io;
+  io.ch = &S.ch; io.st = st; io.hot = hot;
+  io.dec.init(payloads + ds.payload_off, ds.payload_len);
+  io.cab.init(out + ds.out_off, ds.out_cap);
+  io.in_sigmap = 0; io.expect_eob = 0; io.bins = 0; io.done = 0; io.mb_addr = 0;
+  avr::SliceParser<AvrDecodeIO> parser(io, ds.sp, row, ++S.uid);
+  int rc = parser.run();
+  int err = rc < 0 ? AVR_E_CORRUPT : io.cab.err ? io.cab.err : !io.done ? AVR_E_CORRUPT
+            : io.dec.pos > ds.payload_len + 16 ? AVR_E_CORRUPT : AVR_OK;
+  *out_len = io.cab.n; *out_bins = io.bins; *status = err;
+  if (err) S.failed = 1;
+}
+
+// Whole file on one thread (host emulation; the kernel interleaves the cooperative steps itself).
 static AVR_HDN void avr_decompress_chain_body(const AvrFileDesc& fd, const AvrDecSlice* slices_all, const uint8_t* payloads,
                                               uint16_t* est, uint8_t* store0, uint8_t* store1, avr::MbInfo* row,
                                               uint8_t* st, const AvrTables* tab, uint8_t* out, uint32_t* out_len,
                                               uint32_t* out_bins, int* status) {
-  AvrChain ch;
-  ch.init(est, store0, store1, fd.max_mbs, &tab->div);
-  uint32_t uid = 0;
+  AvrDecState S;
+  S.ch.init(est, store0, store1, fd.max_mbs, &tab->hot.div);
+  S.uid = 0; S.failed = 0;
   for (uint32_t s = 0; s < fd.nslices; s++) {
     const AvrDecSlice& ds = slices_all[fd.slice_off + s];
-    if (ds.flip) ch.flip(ds.sp.mb_w, ds.sp.mb_h, ds.flip == 1);
-    if (uid == 0) for (int x = 0; x < ds.sp.mb_w; x++) row[x].uid = 0;
-    AvrDecodeIO io;
-    io.ch = &ch; io.st = st; io.tab = tab;
-    io.dec.init(payloads + ds.payload_off, ds.payload_len);
-    io.cab.init(out + ds.out_off, ds.out_cap);
-    io.in_sigmap = 0; io.expect_eob = 0; io.bins = 0; io.done = 0; io.mb_addr = 0;
-    avr_cabac_init_states(st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp);
-    avr::SliceParser<AvrDecodeIO> parser(io, ds.sp, row, ++uid);
-    int rc = parser.run();
-    int err = rc < 0 ? AVR_E_CORRUPT : io.cab.err ? io.cab.err : !io.done ? AVR_E_CORRUPT
-              : io.dec.pos > ds.payload_len + 16 ? AVR_E_CORRUPT : AVR_OK;
-    out_len[fd.slice_off + s] = io.cab.n;
-    out_bins[fd.slice_off + s] = io.bins;
-    status[fd.slice_off + s] = err;
-    if (err) {   // the model state is meaningless after a failed slice: fail the rest of the file
-      for (uint32_t r = s + 1; r < fd.nslices; r++) { out_len[fd.slice_off + r] = 0; out_bins[fd.slice_off + r] = 0; status[fd.slice_off + r] = AVR_E_CORRUPT; }
-      return;
-    }
+    if (ds.flip) S.ch.flip(ds.sp.mb_w, ds.sp.mb_h, ds.flip == 1);
+    avr_cabac_init_states(st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, 0, 1);
+    avr_decompress_slice(S, ds, payloads, row, st, &tab->hot, out, &out_len[fd.slice_off + s], &out_bins[fd.slice_off + s],
+                         &status[fd.slice_off + s]);
   }
 }

@@ -78,7 +78,9 @@ static AVR_HD void avr_nz_ctx(AvrNzCtx* c, const uint8_t* cur, const uint8_t* pr
 }
 
 struct AvrChain {
-  uint16_t* est;        // [AVR_KEY_COUNT]
+  uint16_t* est;        // [AVR_KEY_COUNT] (global memory)
+  uint16_t* est_def;    // [AVR_NUM_CTX_KEYS] cells of the 1026 default keys: shared memory in the
+                        // decompress kernel (most bins use them), == est otherwise
   uint8_t* store[2];    // [max_mbs * 64] each
   uint32_t max_mbs;
   int cur;
@@ -86,36 +88,43 @@ struct AvrChain {
   const AvrDivTab* dt;
 
   AVR_HD void init(uint16_t* e, uint8_t* s0, uint8_t* s1, uint32_t mbs, const AvrDivTab* d) {
-    est = e; store[0] = s0; store[1] = s1; max_mbs = mbs; cur = 0; mb_w = 1; dt = d;
+    est = e; est_def = e; store[0] = s0; store[1] = s1; max_mbs = mbs; cur = 0; mb_w = 1; dt = d;
   }
+  AVR_HD uint16_t* cell(uint32_t key) { return key < AVR_NUM_CTX_KEYS ? est_def + key : est + key; }
   // update_frame_spec (recode.cpp:831-850) when it flips: the new current picture is zeroed;
   // with a size change both are (prev_valid = 0).
   AVR_HDN void flip(int mb_w_, int mb_h_, int prev_valid) {
     cur ^= 1;
     mb_w = mb_w_;
+    zero_stores(store[cur], prev_valid ? nullptr : store[cur ^ 1], mb_w_, mb_h_, 0, 1);
+  }
+  // lane `lane` of `nlanes` zeroes its share (the decompress kernel calls it with the whole warp)
+  static AVR_HDN void zero_stores(uint8_t* a8, uint8_t* b8, int mb_w_, int mb_h_, int lane, int nlanes) {
     size_t nb = (size_t)mb_w_ * mb_h_ * AVR_MB_STRIDE / 16;
     struct alignas(16) Q { uint64_t a, b; };
-    Q* a = reinterpret_cast<Q*>(store[cur]);
     Q z; z.a = z.b = 0;
-    for (size_t i = 0; i < nb; i++) a[i] = z;
-    if (!prev_valid) {
-      Q* b = reinterpret_cast<Q*>(store[cur ^ 1]);
-      for (size_t i = 0; i < nb; i++) b[i] = z;
+    Q* a = reinterpret_cast<Q*>(a8);
+    for (size_t i = lane; i < nb; i += nlanes) a[i] = z;
+    if (b8) {
+      Q* b = reinterpret_cast<Q*>(b8);
+      for (size_t i = lane; i < nb; i += nlanes) b[i] = z;
     }
   }
   AVR_HD uint8_t* mb(uint32_t mb_addr) { return store[cur] + (size_t)mb_addr * AVR_MB_STRIDE; }
 
   AVR_HD void encode(AvrRangeEnc& enc, uint32_t key, int symbol, uint32_t limit) {
-    uint32_t cell = est[key];
+    uint16_t* c = cell(key);
+    uint32_t cell = *c;
     uint32_t pos = cell & 0xFF, tot = pos + (cell >> 8);
     enc.put(symbol, avr_range_of_1(enc.range, pos, tot, dt));
-    est[key] = (uint16_t)avr_est_update(cell, symbol, limit);
+    *c = (uint16_t)avr_est_update(cell, symbol, limit);
   }
   AVR_HD int decode(AvrRangeDec& dec, uint32_t key, uint32_t limit) {
-    uint32_t cell = est[key];
+    uint16_t* c = cell(key);
+    uint32_t cell = *c;
     uint32_t pos = cell & 0xFF, tot = pos + (cell >> 8);
     int symbol = dec.get(avr_range_of_1(dec.range, pos, tot, dt));
-    est[key] = (uint16_t)avr_est_update(cell, symbol, limit);
+    *c = (uint16_t)avr_est_update(cell, symbol, limit);
     return symbol;
   }
 };

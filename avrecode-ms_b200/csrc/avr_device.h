@@ -82,12 +82,34 @@ struct AvrRangeEnc {
   }
 };
 
+// Input bytes are fetched eight at a time from a 16-byte aligned, zero-padded pool and the next
+// word is requested as soon as the current one is opened, so the load latency is off the per-bin
+// dependency chain.  Bytes at or beyond `size` read as zero (arithmetic_code.h:283).
 struct AvrRangeDec {
   uint64_t low, range;
   const uint8_t* in;
   uint32_t pos, size;
   uint32_t next_digit;
-  AVR_HD uint32_t aligned() { return pos < size ? in[pos++] : (pos++, 0u); }
+  uint64_t w_cur, w_next;
+  AVR_HD uint64_t load_word(uint32_t off) const {
+    if (off >= size) return 0;
+    uint64_t w;
+#if defined(__CUDA_ARCH__)
+    w = *reinterpret_cast<const uint64_t*>(in + off);
+#else
+    w = 0;
+    for (int k = 7; k >= 0; k--) w = (w << 8) | in[off + (uint32_t)k];   // pool is padded: in[off..off+7] is readable
+#endif
+    uint32_t valid = size - off;
+    if (valid < 8) w &= (1ull << (8 * valid)) - 1;
+    return w;
+  }
+  AVR_HD uint32_t aligned() {
+    if ((pos & 7) == 0 && pos) { w_cur = w_next; w_next = load_word(pos + 8); }
+    uint32_t b = (uint32_t)(w_cur >> (8 * (pos & 7))) & 0xFF;
+    pos++;
+    return b;
+  }
   AVR_HD void consume() {
     uint32_t d = aligned();
     uint32_t digit = ((next_digit << 7) | (d >> 1)) & 0xFF;
@@ -95,8 +117,10 @@ struct AvrRangeDec {
     low = (low << 8) + digit;
     range <<= 8;
   }
+  // p must be 8-byte aligned and readable up to ((sz + 15) & ~7) bytes
   AVR_HD void init(const uint8_t* p, uint32_t sz) {
     in = p; pos = 0; size = sz;
+    w_cur = load_word(0); w_next = load_word(8);
     next_digit = aligned();
     low = next_digit >> 1;
     range = 128;

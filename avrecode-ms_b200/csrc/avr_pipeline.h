@@ -254,5 +254,5 @@ static AVR_HDN void avr_body_code(const AvrPipe& a, uint32_t s) {
   const AvrBatchSlice sl = a.bslices[s];
   const uint32_t e0 = a.seg[sl.block_start + s];
   const uint32_t e1 = s + 1 < a.nslices ? a.seg[a.bslices[s + 1].block_start + s + 1] : a.nemit;
-  avr_pass_code(a.prob, e0, e1, &a.tab->div, a.scratch + a.scratch_off[s], a.scratch_cap[s], &a.out_len[s], &a.status[s]);
+  avr_pass_code(a.prob, e0, e1, &a.tab->hot.div, a.scratch + a.scratch_off[s], a.scratch_cap[s], &a.out_len[s], &a.status[s]);
 }
