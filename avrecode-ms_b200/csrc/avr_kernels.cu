@@ -8,6 +8,7 @@
 #include "avr_bodies.h"
 #include "avr_kernels.h"
 #include "avr_pipeline.h"
+#include "avr_decode.h"
 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fds, int nfiles, const uint16_t* bins,
@@ -24,47 +25,46 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
                           scratch_off, scratch_cap, out_len, status);
 }
 
-// One warp per file.  Lane 0 is the chain (strict per-bin dependency); all 32 lanes do the bulk
-// steps between slices (zeroing the picture stores on a flip, CABAC state initialisation, staging
-// the per-bin tables and the 1026 default-key estimators in shared memory).
-struct AvrDecSmem {
-  AvrHotTabs hot;
-  uint16_t est_def[AVR_NUM_CTX_KEYS + 2];
-  uint8_t st[1024];
-};
+// One warp per file.  Lane 0 is the chain (strict per-bin dependency, avr_decode.h); all 32 lanes
+// do the bulk steps between slices: zeroing the picture stores on a flip, CABAC state
+// initialisation, staging the per-bin tables and the default-key estimators in shared memory.
 __global__ void __launch_bounds__(32) avr_k_decompress_chain(const AvrFileDesc* fds, int nfiles, const AvrDecSlice* slices,
                                                              const uint8_t* payloads, uint16_t* est_pool, uint8_t* store_pool,
                                                              avr::MbInfo* row_pool, const AvrTables* tab, uint8_t* out,
                                                              uint32_t* out_len, uint32_t* out_bins, int* status) {
-  __shared__ AvrDecSmem sm;
   const int f = blockIdx.x, lane = threadIdx.x;
   if (f >= nfiles) return;
   const AvrFileDesc fd = fds[f];
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(&tab->hot);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(&sm.hot);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&g_dec.hot);
     for (uint32_t i = lane; i < sizeof(AvrHotTabs) / 4; i += 32) dst[i] = src[i];
-    for (uint32_t i = lane; i < AVR_NUM_CTX_KEYS; i += 32) sm.est_def[i] = AVR_EST_INIT;
+    for (uint32_t i = lane; i < AVR_NUM_CTX_KEYS; i += 32) g_dec.est_def[i] = AVR_EST_INIT;
   }
-  uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
-  uint8_t* s1 = s0 + (size_t)fd.max_mbs * AVR_MB_STRIDE;
-  AvrDecState S;
-  S.ch.init(est_pool + (size_t)f * AVR_KEY_COUNT, s0, s1, fd.max_mbs, &sm.hot.div);
-  S.ch.est_def = sm.est_def;
-  S.uid = 0; S.failed = 0;
+  if (lane == 0) {
+    uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
+    avr_dec_file_begin(est_pool + (size_t)f * AVR_KEY_COUNT, s0, s0 + (size_t)fd.max_mbs * AVR_MB_STRIDE);
+  }
   __syncwarp();
+  uint32_t uid = 0;
+  int failed = 0;
   for (uint32_t s = 0; s < fd.nslices; s++) {
-    const AvrDecSlice& ds = slices[fd.slice_off + s];
-    if (ds.flip) {   // update_frame_spec: same decision in every lane
-      S.ch.cur ^= 1; S.ch.mb_w = ds.sp.mb_w;
-      AvrChain::zero_stores(S.ch.store[S.ch.cur], ds.flip == 1 ? nullptr : S.ch.store[S.ch.cur ^ 1], ds.sp.mb_w, ds.sp.mb_h, lane, 32);
+    const uint32_t g = fd.slice_off + s;
+    const AvrDecSlice& ds = slices[g];
+    if (failed) { if (lane == 0) { out_len[g] = 0; out_bins[g] = 0; status[g] = AVR_E_CORRUPT; } continue; }
+    if (ds.flip) {
+      if (lane == 0) avr_dec_flip_toggle(ds);
+      __syncwarp();
+      avr_dec_flip_zero(ds, lane, 32);
     }
-    avr_cabac_init_states(sm.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, lane, 32);
+    avr_cabac_init_states(g_dec.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, lane, 32);
     __syncwarp();
-    if (lane == 0)
-      avr_decompress_slice(S, ds, payloads, row_pool + fd.mb_base, sm.st, &sm.hot, out, &out_len[fd.slice_off + s],
-                           &out_bins[fd.slice_off + s], &status[fd.slice_off + s]);
-    __syncwarp();
+    int rc = 0;
+    if (lane == 0) {
+      rc = avr_dec_slice(ds, payloads, row_pool + fd.mb_base, ++uid, out, &out_len[g], &out_bins[g]);
+      status[g] = rc;
+    }
+    failed = __shfl_sync(0xFFFFFFFFu, rc, 0) != 0;
   }
 }
 

@@ -13,6 +13,7 @@
 #include "../avrecode-ms_b200/csrc/avr_bodies.h"
 #include "../avrecode-ms_b200/csrc/avr_host_tables.h"
 #include "../avrecode-ms_b200/csrc/avr_pipeline.h"
+#include "../avrecode-ms_b200/csrc/avr_decode.h"
 #include <algorithm>
 
 static bool read_file(const char* fn, std::vector<uint8_t>* out) {
@@ -171,8 +172,8 @@ static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRec
   std::vector<uint32_t> olen(ds.size()), obins(ds.size());
   std::vector<int> status(ds.size());
   pool.resize(pool.size() + 16);
-  avr_decompress_chain_body(fd, ds.data(), pool.data(), est.data(), s0.data(), s1.data(), row.data(), st.data(), &tab,
-                            out.data(), olen.data(), obins.data(), status.data());
+  avr_decompress_file_host(fd, ds.data(), pool.data(), est.data(), s0.data(), s1.data(), row.data(), &tab,
+                           out.data(), olen.data(), obins.data(), status.data());
   int bad = 0;
   uint64_t bins = 0;
   for (size_t s = 0; s < ds.size(); s++) {
