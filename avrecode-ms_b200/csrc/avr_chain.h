@@ -22,8 +22,9 @@
 // significant_coeff_flag ctxIdxInc for frame-coded 8x8 blocks (ITU-T H.264 Table 9-43),
 // the reference's sig_coeff_flag_offset_8x8[0] (recode.cpp:691-696), 4 bits per entry.
 static AVR_HD int avr_sig8x8_off(int zz) {
-  const uint64_t t[4] = {0x5544433445543210ull, 0x789A987776334444ull, 0xB689AE9876BDCB67ull, 0x0CAEBDCB9AE96BDCull};
-  return (int)((t[zz >> 4] >> ((zz & 15) * 4)) & 15);
+  const int q = zz >> 4;   // selects, not an indexed stack array
+  const uint64_t t = q == 0 ? 0x5544433445543210ull : q == 1 ? 0x789A987776334444ull : q == 2 ? 0xB689AE9876BDCB67ull : 0x0CAEBDCB9AE96BDCull;
+  return (int)((t >> ((zz & 15) * 4)) & 15);
 }
 // zigzag offset used in the sig-map key (recode.cpp:704-712)
 static AVR_HD int avr_zz_off(int zz, int size, int is_dc, int c422) {

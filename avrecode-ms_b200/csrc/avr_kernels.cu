@@ -25,46 +25,54 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
                           scratch_off, scratch_cap, out_len, status);
 }
 
-// One warp per file.  Lane 0 is the chain (strict per-bin dependency, avr_decode.h); all 32 lanes
-// do the bulk steps between slices: zeroing the picture stores on a flip, CABAC state
-// initialisation, staging the per-bin tables and the default-key estimators in shared memory.
-__global__ void __launch_bounds__(32) avr_k_decompress_chain(const AvrFileDesc* fds, int nfiles, const AvrDecSlice* slices,
-                                                             const uint8_t* payloads, uint16_t* est_pool, uint8_t* store_pool,
-                                                             avr::MbInfo* row_pool, const AvrTables* tab, uint8_t* out,
-                                                             uint32_t* out_len, uint32_t* out_bins, int* status) {
-  const int f = blockIdx.x, lane = threadIdx.x;
+// One block (two warps) per file.  Thread 0 is the chain (strict per-bin dependency), thread 32 is
+// the CABAC encoder fed through a shared-memory ring (avr_decode.h); all 64 threads do the bulk
+// steps between slices: zeroing the picture stores on a flip, CABAC state initialisation, staging
+// the per-bin tables and the default-key estimators in shared memory.
+#define AVR_DEC_THREADS 64
+__global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
+    const AvrFileDesc* fds, int nfiles, const AvrDecSlice* slices, const uint8_t* payloads, uint16_t* est_pool,
+    uint8_t* store_pool, avr::MbInfo* row_pool, const AvrTables* tab, uint8_t* out, uint32_t* out_len, uint32_t* out_bins,
+    int* status) {
+  __shared__ int s_failed;
+  const int f = blockIdx.x, tid = threadIdx.x;
   if (f >= nfiles) return;
   const AvrFileDesc fd = fds[f];
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(&tab->hot);
     uint32_t* dst = reinterpret_cast<uint32_t*>(&g_dec.hot);
-    for (uint32_t i = lane; i < sizeof(AvrHotTabs) / 4; i += 32) dst[i] = src[i];
-    for (uint32_t i = lane; i < AVR_NUM_CTX_KEYS; i += 32) g_dec.est_def[i] = AVR_EST_INIT;
+    for (uint32_t i = tid; i < sizeof(AvrHotTabs) / 4; i += AVR_DEC_THREADS) dst[i] = src[i];
+    for (uint32_t i = tid; i < AVR_NUM_CTX_KEYS; i += AVR_DEC_THREADS) g_dec.est_def[i] = AVR_EST_INIT;
+    for (uint32_t i = tid; i < AVR_RING; i += AVR_DEC_THREADS) g_dec.ring[i] = 0;
   }
-  if (lane == 0) {
+  if (tid == 0) {
     uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
     avr_dec_file_begin(est_pool + (size_t)f * AVR_KEY_COUNT, s0, s0 + (size_t)fd.max_mbs * AVR_MB_STRIDE);
+    s_failed = 0;
   }
-  __syncwarp();
+  __syncthreads();
   uint32_t uid = 0;
-  int failed = 0;
   for (uint32_t s = 0; s < fd.nslices; s++) {
     const uint32_t g = fd.slice_off + s;
     const AvrDecSlice& ds = slices[g];
-    if (failed) { if (lane == 0) { out_len[g] = 0; out_bins[g] = 0; status[g] = AVR_E_CORRUPT; } continue; }
+    if (s_failed) { if (tid == 0) { out_len[g] = 0; out_bins[g] = 0; status[g] = AVR_E_CORRUPT; } continue; }
     if (ds.flip) {
-      if (lane == 0) avr_dec_flip_toggle(ds);
-      __syncwarp();
-      avr_dec_flip_zero(ds, lane, 32);
+      if (tid == 0) avr_dec_flip_toggle(ds);
+      __syncthreads();
+      avr_dec_flip_zero(ds, tid, AVR_DEC_THREADS);
     }
-    avr_cabac_init_states(g_dec.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, lane, 32);
-    __syncwarp();
+    avr_cabac_init_states(g_dec.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, tid, AVR_DEC_THREADS);
+    __syncthreads();
     int rc = 0;
-    if (lane == 0) {
-      rc = avr_dec_slice(ds, payloads, row_pool + fd.mb_base, ++uid, out, &out_len[g], &out_bins[g]);
-      status[g] = rc;
+    if (tid == 0) rc = avr_dec_slice(ds, payloads, row_pool + fd.mb_base, ++uid, &out_bins[g]);
+    else if (tid == 32) avr_cab_encoder_thread(out + ds.out_off, ds.out_cap);
+    __syncthreads();
+    if (tid == 0) {
+      if (!rc) rc = g_dec.cab_err;
+      out_len[g] = g_dec.cab_n; status[g] = rc;
+      if (rc) s_failed = 1;
     }
-    failed = __shfl_sync(0xFFFFFFFFu, rc, 0) != 0;
+    __syncthreads();
   }
 }
 
@@ -119,7 +127,7 @@ int avr_launch_compress_chain(const AvrDevBatch& b, cudaStream_t st) {
 
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
   if (b.nfiles == 0) return 0;
-  avr_k_decompress_chain<<<b.nfiles, 32, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
+  avr_k_decompress_chain<<<b.nfiles, AVR_DEC_THREADS, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
                                                  b.tab, b.out, b.out_len, b.out_bins, b.status);
   return (int)cudaGetLastError();
 }

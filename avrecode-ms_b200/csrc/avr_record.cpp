@@ -13,6 +13,8 @@ namespace avr {
 namespace {
 
 struct RecordIO {
+  static constexpr bool kFastResidual = false;
+  int residual_block(int, int, int, int, int, int, int) { return 0; }
   CabacDecoder dec;
   uint8_t st[1024];
   Recorder& rec;

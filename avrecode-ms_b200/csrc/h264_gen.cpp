@@ -52,6 +52,8 @@ void append_nal(std::vector<uint8_t>* out, int long_sc, int nal_ref_idc, int nal
 }
 
 struct GenIO {
+  static constexpr bool kFastResidual = false;
+  int residual_block(int, int, int, int, int, int, int) { return 0; }
   const GenParams& gp;
   Rng& rng;
   CabacEncoder enc;

@@ -13,6 +13,8 @@
 //     void mb_begin(x, y)             -- ModelHooks::mb_xy
 //     void sub_mb_begin(cat,n,max_coeff,is_dc,c422) / sub_mb_end()  -- begin_sub_mb / end_sub_mb
 //     void sigmap_begin() / sigmap_end()   -- begin/end_coding_type(PIP_SIGNIFICANCE_MAP)
+//     static constexpr bool kFastResidual; int residual_block(cat,n,max_coeff,is_dc,sig,last,abs)
+//                                     -- optional whole-block entry point (see residual_block below)
 //     void hint(kind, arg)            -- no reference counterpart; lets the synthetic generator
 //                                        keep random bins legal (no-op in the product policies)
 // Policies: host CABAC decode + record (compress front end), device range decode + CABAC
@@ -206,6 +208,9 @@ struct SliceParser {
     const int sig_base[6] = {105, 120, 134, 149, 152, 402};
     const int last_base[6] = {166, 181, 195, 210, 213, 417};
     const int abs_base[6] = {227, 237, 247, 257, 266, 426};
+    // a policy may take the whole block in one call (the decompress kernel keeps its decoder
+    // registers live across the block's bins: avr_decode.h)
+    if constexpr (IO::kFastResidual) return io.residual_block(cat, n, max_coeff, is_dc, sig_base[cat], last_base[cat], abs_base[cat]);
     io.sub_mb_begin(cat, n, max_coeff, is_dc, 0);
     io.sigmap_begin();
     int coeff_count = 0;
@@ -257,8 +262,9 @@ struct SliceParser {
 
   static AVR_HD int sig8x8_inc(int i) {
     // Table 9-43, frame coded: significant_coeff_flag ctxIdxInc for 8x8 blocks, 4 bits each
-    const uint64_t t[4] = {0x5544433445543210ull, 0x789A987776334444ull, 0xB689AE9876BDCB67ull, 0x0CAEBDCB9AE96BDCull};
-    return (int)((t[i >> 4] >> ((i & 15) * 4)) & 15);
+    const int q = i >> 4;   // selects, not an indexed stack array
+    const uint64_t t = q == 0 ? 0x5544433445543210ull : q == 1 ? 0x789A987776334444ull : q == 2 ? 0xB689AE9876BDCB67ull : 0x0CAEBDCB9AE96BDCull;
+    return (int)((t >> ((i & 15) * 4)) & 15);
   }
   static AVR_HD int last8x8_inc(int i) {
     // Table 9-43: last_significant_coeff_flag ctxIdxInc for 8x8 blocks
