@@ -130,7 +130,7 @@ AVR_DEC_INL int avr_cab_consume(AvrCabRegs& c, uint32_t rec) {
 
 // ---- ring -----------------------------------------------------------------------------------------
 AVR_DEC_INL void avr_ring_post(uint32_t ctx, int symbol) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDACC__)
   const uint32_t head = g_dec.ring_head;
   if (head - g_dec.ring_tail_seen >= AVR_RING - 1) {          // full: wait for the encoder
     uint32_t t;
@@ -169,7 +169,7 @@ static __device__ __noinline__ void avr_cab_encoder_thread(uint8_t* out, uint32_
 AVR_DEC_INL uint64_t avr_dec_load_word(uint32_t off) {
   if (off >= g_dec.size) return 0;
   uint64_t w;
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDACC__)
   w = __ldg(reinterpret_cast<const unsigned long long*>(g_dec.in + off));
 #else
   w = 0;
