@@ -145,6 +145,23 @@ AVR_DEC_INL void avr_ring_post(uint32_t ctx, int symbol) {
 #endif
 }
 
+// same, with the producer cursor kept in the caller's registers (residual blocks)
+AVR_DEC_INL void avr_ring_post_r(uint32_t& head, uint32_t& tail_seen, uint32_t ctx, int symbol) {
+#if defined(__CUDACC__)
+  if (head - tail_seen >= AVR_RING - 1) {
+    uint32_t t;
+    do { t = g_dec.ring_tail; } while (head - t >= AVR_RING - 1);
+    tail_seen = t;
+  }
+  const uint32_t tag = ((head >> AVR_RING_LOG) + 1) & 0xFFFF;
+  reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (tag << 16) | (ctx << 1) | (uint32_t)symbol;
+  head++;
+#else
+  (void)head; (void)tail_seen;
+  avr_cab_consume(g_cab_host, (ctx << 1) | (uint32_t)symbol);
+#endif
+}
+
 #if defined(__CUDACC__)
 // Encoder thread: consumes the slice's records until end_of_slice / abort.
 static __device__ __noinline__ void avr_cab_encoder_thread(uint8_t* out, uint32_t cap) {
@@ -181,7 +198,10 @@ AVR_DEC_INL uint64_t avr_dec_load_word(uint32_t off) {
 }
 // input bytes come eight at a time; the next word is requested when the current one is opened
 // so its latency is off the per-bin dependency chain.  Rare (about once per 8 bins): not inlined.
-AVR_DEC_FN void avr_dec_refill(uint64_t& low, uint64_t& range, uint64_t target) {
+struct AvrLowRange { uint64_t low, range; };
+// by value in, by value out: a reference parameter of a non-inlined function would pin the
+// caller's low/range to local memory (seen as LDL/STL per bin in profiles/r01_*_v3)
+AVR_DEC_FN AvrLowRange avr_dec_refill(uint64_t low, uint64_t range, uint64_t target) {
   while (range < target) {
     const uint32_t pos = g_dec.pos;
     if ((pos & 7) == 0 && pos) { g_dec.w_cur = g_dec.w_next; g_dec.w_next = avr_dec_load_word(pos + 8); }
@@ -192,14 +212,16 @@ AVR_DEC_FN void avr_dec_refill(uint64_t& low, uint64_t& range, uint64_t target) 
     low = (low << 8) + digit;
     range <<= 8;
   }
+  AvrLowRange r; r.low = low; r.range = range;
+  return r;
 }
 AVR_DEC_INL void avr_dec_init_range(const uint8_t* p, uint32_t sz) {
   g_dec.in = p; g_dec.size = sz;
   g_dec.w_cur = avr_dec_load_word(0); g_dec.w_next = avr_dec_load_word(8);
   g_dec.next_digit = (uint32_t)g_dec.w_cur & 0xFF; g_dec.pos = 1;
   uint64_t low = g_dec.next_digit >> 1, range = 128;
-  avr_dec_refill(low, range, 1ull << 63);   // 7 digits: range 2^7 -> 2^63 (arithmetic_code.h:226-228)
-  g_dec.low = low; g_dec.range = range;
+  const AvrLowRange r = avr_dec_refill(low, range, 1ull << 63);   // 7 digits: range 2^7 -> 2^63 (arithmetic_code.h:226-228)
+  g_dec.low = r.low; g_dec.range = r.range;
 }
 // one symbol with estimator cell `cell` (recode.cpp:823-827 + arithmetic_code.h:232-248)
 AVR_DEC_INL int avr_dec_symbol(uint64_t& low, uint64_t& range, uint32_t cell) {
@@ -208,7 +230,7 @@ AVR_DEC_INL int avr_dec_symbol(uint64_t& low, uint64_t& range, uint32_t cell) {
   const uint64_t r0 = range - r1;
   const int symbol = low >= r0;
   if (symbol) { low -= r0; range = r1; } else { range = r0; }
-  if (range < (1ull << 51) && range != 0) avr_dec_refill(low, range, 1ull << 55);
+  if (range < (1ull << 51) && range != 0) { const AvrLowRange r = avr_dec_refill(low, range, 1ull << 55); low = r.low; range = r.range; }
   return symbol;
 }
 // estimator update on the packed cell (pos | neg << 8), recode.cpp:1037-1054
@@ -263,7 +285,7 @@ AVR_DEC_FN int avr_dec_terminate() {
 // low/range stay in registers for the whole block.  Returns coeff_count.
 AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, int sig_base, int last_base, int abs_base) {
   uint64_t low = g_dec.low, range = g_dec.range;
-  uint32_t bins = 0;
+  uint32_t bins = 0, head = g_dec.ring_head, tail_seen = g_dec.ring_tail_seen;
   // nnz bits first.  The count is recovered completely (a block that codes as 0 in 2/4 bits is a
   // full one) so that the store holds what the COMPRESSOR held.
   AvrNzCtx nc;
@@ -283,12 +305,12 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
       last_ctx = last_base + (last == 0 ? 0 : last < 16 ? 1 : last < 32 ? 2 : last < 40 ? 3 : last < 48 ? 4 : last < 52 ? 5 : last < 56 ? 6 : last < 60 ? 7 : 8);
     }
     const int sig = avr_dec_global(low, range, key0 + (uint32_t)coeff_count * 16u + (uint32_t)zz_off, 0x50);
-    avr_ring_post((uint32_t)sig_ctx, sig);
+    avr_ring_post_r(head, tail_seen, (uint32_t)sig_ctx, sig);
     bins++;
     if (sig) {
       coeff_count++;
       const int eob = (stored == coeff_count);                 // inferred, never range-coded
-      avr_ring_post((uint32_t)last_ctx, eob);
+      avr_ring_post_r(head, tail_seen, (uint32_t)last_ctx, eob);
       bins++;
       if (eob) { last = max_coeff; break; }
     }
@@ -305,7 +327,7 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
   for (int c = coeff_count; c > 0; c--) {
     const int ctx1 = abs_base + (node_ctx < 4 ? node_ctx + 1 : 0);
     const int b0 = avr_dec_default(low, range, (uint32_t)ctx1);
-    avr_ring_post((uint32_t)ctx1, b0);
+    avr_ring_post_r(head, tail_seen, (uint32_t)ctx1, b0);
     bins++;
     if (b0 == 0) {
       node_ctx = node_ctx < 3 ? node_ctx + 1 : node_ctx;
@@ -316,7 +338,7 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
       int coeff_abs = 2;
       while (coeff_abs < 15) {
         const int b = avr_dec_default(low, range, (uint32_t)ctx2);
-        avr_ring_post((uint32_t)ctx2, b);
+        avr_ring_post_r(head, tail_seen, (uint32_t)ctx2, b);
         bins++;
         if (!b) break;
         coeff_abs++;
@@ -325,23 +347,24 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
         int j = 0;
         for (;;) {
           const int b = avr_dec_default(low, range, AVR_CTX_BYPASS);
-          avr_ring_post(AVR_CTX_BYPASS, b);
+          avr_ring_post_r(head, tail_seen, AVR_CTX_BYPASS, b);
           bins++;
           if (!b || j >= 30) break;
           j++;
         }
         while (j--) {
           const int b = avr_dec_default(low, range, AVR_CTX_BYPASS);
-          avr_ring_post(AVR_CTX_BYPASS, b);
+          avr_ring_post_r(head, tail_seen, AVR_CTX_BYPASS, b);
           bins++;
         }
       }
     }
     const int sgn = avr_dec_default(low, range, AVR_CTX_BYPASS);
-    avr_ring_post(AVR_CTX_BYPASS, sgn);
+    avr_ring_post_r(head, tail_seen, AVR_CTX_BYPASS, sgn);
     bins++;
   }
   g_dec.low = low; g_dec.range = range;
+  g_dec.ring_head = head; g_dec.ring_tail_seen = tail_seen;
   g_dec.bins += bins;
   return coeff_count;
 }

@@ -185,9 +185,18 @@ __global__ void __launch_bounds__(256) avr_k_estimate(const uint32_t* sorted, co
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) avr_body_estimate(i, sorted, idx, head, P, fn, prob);
 }
+// thread per slice: the one inherently serial pass.  The exact-division table is staged in shared
+// memory (indexed by the data-dependent total, different in every lane).
 __global__ void __launch_bounds__(32) avr_k_code(AvrPipe a) {
+  __shared__ AvrDivTab dt;
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&a.tab->hot.div);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&dt);
+    for (uint32_t i = threadIdx.x; i < sizeof(AvrDivTab) / 4; i += 32) dst[i] = src[i];
+  }
+  __syncwarp();
   uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < a.nslices) avr_body_code(a, s);
+  if (s < a.nslices) avr_body_code(a, s, &dt);
 }
 
 size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bit) {

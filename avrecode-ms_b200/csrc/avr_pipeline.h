@@ -147,14 +147,26 @@ static AVR_HD uint32_t avr_half_apply(AvrHalf f, uint32_t pos) { return (pos + f
 static AVR_HD uint16_t avr_prob_pack(uint32_t sym, uint32_t pos, uint32_t total) { return (uint16_t)(sym | (pos << 1) | (total << 8)); }
 
 // ---- pass D: one slice ------------------------------------------------------------------------
+// prob[] is read four records (one 8-byte word) at a time and the next word is requested before
+// the current one is coded, so the load latency stays off the low/range dependency chain.
 static AVR_HDN void avr_pass_code(const uint16_t* prob, uint32_t e0, uint32_t e1, const AvrDivTab* dt, uint8_t* scratch,
                                   uint32_t cap, uint32_t* out_len, int* status) {
   AvrRangeEnc enc;
   enc.init(scratch, cap);
-  for (uint32_t e = e0; e < e1; e++) {
-    uint32_t r = prob[e];
-    enc.put((int)(r & 1), avr_range_of_1(enc.range, (r >> 1) & 0x7F, r >> 8, dt));
+  uint32_t e = e0;
+#define AVR_CODE_STEP(r_) do { const uint32_t r__ = (uint32_t)(r_); \
+    enc.put((int)(r__ & 1), avr_range_of_1(enc.range, (r__ >> 1) & 0x7F, (r__ >> 8) & 0x7F, dt)); } while (0)
+  while (e < e1 && (e & 3)) { AVR_CODE_STEP(prob[e]); e++; }
+  const uint64_t* p = reinterpret_cast<const uint64_t*>(prob + e);
+  uint64_t nxt = e + 4 <= e1 ? p[0] : 0;
+  while (e + 4 <= e1) {
+    const uint64_t w = nxt;
+    p++; e += 4;
+    if (e + 4 <= e1) nxt = p[0];
+    AVR_CODE_STEP(w & 0xFFFF); AVR_CODE_STEP((w >> 16) & 0xFFFF); AVR_CODE_STEP((w >> 32) & 0xFFFF); AVR_CODE_STEP(w >> 48);
   }
+  while (e < e1) { AVR_CODE_STEP(prob[e]); e++; }
+#undef AVR_CODE_STEP
   enc.finish();
   *out_len = enc.n;
   *status = enc.err;
@@ -250,9 +262,9 @@ static AVR_HD void avr_body_estimate(uint32_t i, const uint32_t* sorted, const u
   prob[idx[i]] = avr_prob_pack(sym, pos0 + ob, avr_total_at(r, p));
 }
 
-static AVR_HDN void avr_body_code(const AvrPipe& a, uint32_t s) {
+static AVR_HDN void avr_body_code(const AvrPipe& a, uint32_t s, const AvrDivTab* dt) {
   const AvrBatchSlice sl = a.bslices[s];
   const uint32_t e0 = a.seg[sl.block_start + s];
   const uint32_t e1 = s + 1 < a.nslices ? a.seg[a.bslices[s + 1].block_start + s + 1] : a.nemit;
-  avr_pass_code(a.prob, e0, e1, &a.tab->hot.div, a.scratch + a.scratch_off[s], a.scratch_cap[s], &a.out_len[s], &a.status[s]);
+  avr_pass_code(a.prob, e0, e1, dt, a.scratch + a.scratch_off[s], a.scratch_cap[s], &a.out_len[s], &a.status[s]);
 }

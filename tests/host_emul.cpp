@@ -132,7 +132,7 @@ static int compress_pipeline(const std::vector<const avr::FileRecord*>& recs, co
   }
   std::vector<uint8_t> scratch(total + 16);
   a.scratch = scratch.data(); a.scratch_off = soff.data(); a.scratch_cap = scap.data(); a.out_len = olen.data(); a.status = status.data();
-  for (uint32_t s = 0; s < a.nslices; s++) avr_body_code(a, s);
+  for (uint32_t s = 0; s < a.nslices; s++) avr_body_code(a, s, &tab.hot.div);
   out->resize(recs.size());
   for (uint32_t s = 0; s < a.nslices; s++) {
     if (status[s]) { fprintf(stderr, "slice %u status %d\n", s, status[s]); return status[s]; }
