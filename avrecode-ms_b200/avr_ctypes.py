@@ -19,7 +19,7 @@ EXPORTS = [
     "avr_record_new", "avr_record_free", "avr_rec_frame_spec", "avr_rec_slice_begin", "avr_rec_slice_end",
     "avr_rec_mb_xy", "avr_rec_begin_sub_mb", "avr_rec_end_sub_mb", "avr_rec_begin_coding_type",
     "avr_rec_end_coding_type", "avr_rec_bin", "avr_record_annexb", "avr_record_counts", "avr_record_span",
-    "avr_cbatch_create", "avr_cbatch_run", "avr_cbatch_fetch", "avr_cbatch_payload", "avr_cbatch_timing",
+    "avr_cbatch_create", "avr_cbatch_create_files", "avr_cbatch_span_count", "avr_cbatch_span", "avr_cbatch_run", "avr_cbatch_fetch", "avr_cbatch_payload", "avr_cbatch_timing",
     "avr_cbatch_destroy", "avr_dbatch_create", "avr_dbatch_run", "avr_dbatch_fetch", "avr_dbatch_slice",
     "avr_dbatch_timing", "avr_dbatch_destroy", "avr_compress_files", "avr_decompress_files", "avr_buffer_free",
 ]
@@ -40,7 +40,8 @@ class DSlice(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("h2d_ms", C.c_double), ("kernel_ms", C.c_double), ("d2h_ms", C.c_double),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("bins", C.c_uint64),
-                ("coded_symbols", C.c_uint64), ("launches", C.c_uint32), ("coder_launch_ms_x1000", C.c_uint32)]
+                ("coded_symbols", C.c_uint64), ("launches", C.c_uint32), ("coder_launch_ms_x1000", C.c_uint32),
+                ("parse_ms", C.c_double), ("host_ms", C.c_double)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -73,6 +74,11 @@ def lib():
         L.avr_record_span.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32),
                                       C.POINTER(C.c_int32), C.POINTER(C.c_uint32), C.POINTER(SliceParams)]
         L.avr_cbatch_create.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p)]
+        L.avr_cbatch_create_files.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_int, C.c_int,
+                                              C.POINTER(C.c_void_p), C.POINTER(C.c_int)]
+        L.avr_cbatch_span_count.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint32)]
+        L.avr_cbatch_span.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint32),
+                                      C.POINTER(C.c_int32)]
         L.avr_cbatch_run.argtypes = [C.c_void_p, C.c_int]
         L.avr_cbatch_fetch.argtypes = [C.c_void_p]
         L.avr_cbatch_payload.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.POINTER(C.POINTER(C.c_uint8)),
@@ -146,10 +152,32 @@ class Record:
 
 
 class CBatch:
-    def __init__(self, ctx: Context, records):
-        self.records = records
-        arr = (C.c_void_p * len(records))(*[r.h for r in records])
+    def __init__(self, ctx: Context, records=None, files=None, threads=0):
+        """records: list of Record (host parse)  |  files: list of bytes (device-side parse)"""
         self.h = C.c_void_p()
+        if files is not None:
+            n = len(files)
+            self._files = files
+            ins = (C.c_char_p * n)(*files)
+            lens = (C.c_size_t * n)(*[len(b) for b in files])
+            st = (C.c_int * n)()
+            _check(lib().avr_cbatch_create_files(ctx.h, ins, lens, n, threads or (os.cpu_count() or 1), C.byref(self.h), st))
+            self.file_status = list(st)
+            self.records = None
+            self.nslices = []
+            for f in range(n):
+                c = C.c_uint32()
+                _check(lib().avr_cbatch_span_count(self.h, f, C.byref(c)))
+                k = 0
+                for i in range(c.value):
+                    idx = C.c_int32()
+                    lib().avr_cbatch_span(self.h, f, i, None, None, C.byref(idx))
+                    k += idx.value >= 0
+                self.nslices.append(k)
+            return
+        self.records = records
+        self.nslices = [r.slices for r in records]
+        arr = (C.c_void_p * len(records))(*[r.h for r in records])
         _check(lib().avr_cbatch_create(ctx.h, arr, len(records), C.byref(self.h)))
 
     def run(self, mode=MODE_PIPELINE):
@@ -164,7 +192,7 @@ class CBatch:
         return C.string_at(p, n.value)
 
     def payloads(self):
-        return [[self.payload(f, s) for s in range(r.slices)] for f, r in enumerate(self.records)]
+        return [[self.payload(f, s) for s in range(k)] for f, k in enumerate(self.nslices)]
 
     def timing(self):
         t = Timing()

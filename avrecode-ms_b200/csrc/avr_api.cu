@@ -156,6 +156,7 @@ struct avr_cbatch {
   std::vector<uint8_t> h_out;
   uint64_t scratch_bytes = 0, pic_mbs = 0, chain_mbs = 0;
   bool have_pipe = false, have_chain = false;
+  uint32_t create_launches = 0;           // kernels launched by avr_cbatch_create_files (parse, block gather)
   avr_timing t;
   bool ran = false, fetched = false;
   // device-side mutable pointers kept for fetch
@@ -271,6 +272,7 @@ extern "C" int avr_cbatch_run(avr_cbatch* b, int mode) {
     TRY(m.alloc(&tmp, d.cub_tmp_bytes)); d.cub_tmp = tmp;
     b->have_pipe = true;
   }
+  if (mode == AVR_MODE_CHAIN && !d.slices) { avr_set_error("chain mode needs a batch made from host records"); return AVR_E_ARG; }
   if (mode == AVR_MODE_CHAIN && !b->have_chain) {
     TRY(m.alloc(&d.est_pool, (size_t)d.nfiles * AVR_KEY_COUNT));
     TRY(m.alloc(&d.store_pool, (size_t)b->chain_mbs * AVR_MB_STRIDE + 64));
@@ -294,7 +296,7 @@ extern "C" int avr_cbatch_run(avr_cbatch* b, int mode) {
   if (e != cudaSuccess) { avr_set_error("compress kernels: %s", cudaGetErrorString(e)); return AVR_E_CUDA; }
   b->t.kernel_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
   b->t.coder_launch_ms_x1000 = (uint32_t)(ev_ms(ctx->ev[2], ctx->ev[3]) * 1000.0f);
-  b->t.launches = (uint32_t)launches;
+  b->t.launches = (uint32_t)launches + b->create_launches;
   b->ran = true; b->fetched = false;
   return AVR_OK;
 }
@@ -338,8 +340,10 @@ extern "C" int avr_cbatch_payload(const avr_cbatch* b, int file, uint32_t slice,
   return AVR_OK;
 }
 extern "C" void avr_cbatch_timing(const avr_cbatch* b, avr_timing* t) { if (b && t) *t = b->t; }
+void avr_cbatch_files_release(avr_cbatch* b);
 extern "C" void avr_cbatch_destroy(avr_cbatch* b) {
   if (!b) return;
+  avr_cbatch_files_release(b);
   cudaSetDevice(b->ctx->device);
   b->mem.release();
   delete b;
@@ -485,4 +489,188 @@ extern "C" void avr_dbatch_destroy(avr_dbatch* b) {
   cudaSetDevice(b->ctx->device);
   b->mem.release();
   delete b;
+}
+
+// ---- compress batch from raw files: device-side parse (avr_parse.h) ---------------------------
+#include <atomic>
+#include <chrono>
+#include <thread>
+#include "avr_parse.h"
+
+namespace {
+template <class F>
+void par_for(int n, int threads, F&& f) {
+  if (threads <= 1 || n <= 1) { for (int i = 0; i < n; i++) f(i); return; }
+  std::atomic<int> next(0);
+  std::vector<std::thread> th;
+  for (int t = 0; t < (threads < n ? threads : n); t++) th.emplace_back([&] { for (int i; (i = next.fetch_add(1)) < n;) f(i); });
+  for (auto& t : th) t.join();
+}
+double wall_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+}  // namespace
+
+struct AvrFileScan {
+  avr::FileRecord rec;                  // spans, frames (no bins)
+  std::vector<avr::ScanSlice> coded;
+  int rc = 0;
+};
+// kept by the batch for container building
+struct avr_cbatch_files { std::vector<AvrFileScan> scans; };
+static std::vector<std::pair<avr_cbatch*, avr_cbatch_files*>>& files_registry() { static std::vector<std::pair<avr_cbatch*, avr_cbatch_files*>> r; return r; }
+
+extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* files, const size_t* lens, int nfiles,
+                                       int host_threads, avr_cbatch** out, int* file_status) {
+  if (!ctx || !files || !lens || nfiles < 0 || !out || !file_status) return AVR_E_ARG;
+  if (nfiles > 1024) { avr_set_error("at most 1024 files per batch (sort key has 10 file bits)"); return AVR_E_ARG; }
+  CU(cudaSetDevice(ctx->device));
+  const double t_host0 = wall_ms();
+  avr_cbatch_files* bf = new avr_cbatch_files();
+  bf->scans.resize((size_t)nfiles);
+  par_for(nfiles, host_threads, [&](int f) {
+    AvrFileScan& sc = bf->scans[f];
+    sc.rc = avr::scan_annexb(files[f], lens[f], &sc.rec, &sc.coded);
+    if (!sc.rc && sc.rec.out_of_domain) sc.rc = AVR_E_UNSUPPORTED;
+  });
+  // layout of the pools
+  std::vector<AvrParseSlice> ps; std::vector<uint64_t> row_off; std::vector<int> ps_file;
+  std::vector<uint64_t> raw_base((size_t)nfiles, 0);
+  uint64_t raw_bytes = 0, bin_pool = 0, blk_pool = 0, rows = 0;
+  for (int f = 0; f < nfiles; f++) {
+    file_status[f] = bf->scans[f].rc;
+    if (file_status[f]) continue;
+    raw_base[f] = raw_bytes; raw_bytes += (lens[f] + 31) & ~15ull;
+    for (const avr::ScanSlice& c : bf->scans[f].coded) {
+      AvrParseSlice p; memset(&p, 0, sizeof p);
+      p.raw_off = raw_base[f] + c.raw_off; p.size = c.size; memcpy(p.tail, c.tail, 4);
+      // records per CABAC byte: ~11 bins typical; skip runs cost ~2 bins per macroblock and almost no bytes
+      const uint32_t mbs = (uint32_t)c.sp.mb_w * (uint32_t)c.sp.mb_h;
+      p.bin_cap = 24u * c.size + 4u * (mbs > (uint32_t)c.sp.first_mb ? mbs - (uint32_t)c.sp.first_mb : 0u) + 2048u; p.blk_cap = p.bin_cap / 4;
+      p.bin_off = bin_pool; bin_pool += p.bin_cap; p.blk_off = blk_pool; blk_pool += p.blk_cap;
+      p.frame = c.frame; p.sp = c.sp;
+      ps.push_back(p); ps_file.push_back(f); row_off.push_back(rows); rows += (uint64_t)c.sp.mb_w;
+    }
+  }
+  avr_cbatch* b = new avr_cbatch();
+  b->ctx = ctx; memset(&b->d, 0, sizeof b->d); memset(&b->t, 0, sizeof b->t);
+  DevMem& m = b->mem;
+  DevMem tmp;   // freed before returning
+  auto fail = [&](int r) { tmp.release(); m.release(); delete b; delete bf; return r; };
+  const uint32_t ns = (uint32_t)ps.size();
+  uint8_t* d_raw; uint16_t* d_bins; AvrBlock* d_blkpool; avr::MbInfo* d_rows; uint64_t* d_row_off; AvrParseSlice* d_ps; AvrParseResult* d_res;
+  int rc;
+  if ((rc = tmp.alloc(&d_raw, raw_bytes + 64)) || (rc = m.alloc(&d_bins, bin_pool)) || (rc = tmp.alloc(&d_blkpool, blk_pool)) ||
+      (rc = tmp.alloc(&d_rows, rows)) || (rc = tmp.alloc(&d_row_off, ns)) || (rc = tmp.alloc(&d_ps, ns)) || (rc = tmp.alloc(&d_res, ns)))
+    return fail(rc);
+  cudaStream_t st = ctx->stream;
+  // file-local bin numbering = position in the file's region of the bins pool
+  {
+    uint64_t file_first = 0; int cur = -1;
+    for (uint32_t s = 0; s < ns; s++) {
+      if (ps_file[s] != cur) { cur = ps_file[s]; file_first = ps[s].bin_off; }
+      ps[s].file_bin_base = (uint32_t)(ps[s].bin_off - file_first);
+    }
+  }
+  uint64_t h2d = 0;
+  cudaEventRecord(ctx->ev[0], st);
+  for (int f = 0; f < nfiles; f++)
+    if (!file_status[f] && lens[f]) { cudaMemcpyAsync(d_raw + raw_base[f], files[f], lens[f], cudaMemcpyHostToDevice, st); h2d += lens[f]; }
+  cudaMemcpyAsync(d_ps, ps.data(), ns * sizeof(AvrParseSlice), cudaMemcpyHostToDevice, st); h2d += ns * sizeof(AvrParseSlice);
+  cudaMemcpyAsync(d_row_off, row_off.data(), ns * sizeof(uint64_t), cudaMemcpyHostToDevice, st); h2d += ns * 8;
+  cudaEventRecord(ctx->ev[1], st);
+  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, st);
+  cudaEventRecord(ctx->ev[2], st);
+  if (rc) { avr_set_error("parse launch: %s", cudaGetErrorString((cudaError_t)rc)); return fail(AVR_E_CUDA); }
+  std::vector<AvrParseResult> res(ns);
+  cudaMemcpyAsync(res.data(), d_res, ns * sizeof(AvrParseResult), cudaMemcpyDeviceToHost, st);
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess) { avr_set_error("parse kernel: %s", cudaGetErrorString(e)); return fail(AVR_E_CUDA); }
+  b->t.h2d_ms = ev_ms(ctx->ev[0], ctx->ev[1]); b->t.parse_ms = ev_ms(ctx->ev[1], ctx->ev[2]); b->t.launches = 1;
+  // files with a failed slice drop out of the batch
+  for (uint32_t s = 0; s < ns; s++) if (res[s].status && !file_status[ps_file[s]]) file_status[ps_file[s]] = res[s].status;
+  // dense layout of what remains
+  std::vector<AvrFileDesc> fds((size_t)nfiles);
+  std::vector<AvrBatchSlice> bsl; std::vector<AvrFrame> frames;
+  std::vector<uint64_t> soff; std::vector<uint32_t> scap, blk_cnt(ns, 0), blk_dst(ns, 0);
+  uint64_t nblocks = 0, emitted = 0, pic_mbs = 0, scratch = 0, nbins = 0;
+  uint32_t s = 0;
+  for (int f = 0; f < nfiles; f++) {
+    AvrFileDesc& fd = fds[f]; memset(&fd, 0, sizeof fd);
+    const AvrFileScan& sc = bf->scans[f];
+    b->file_slice_off.push_back((uint32_t)bsl.size());
+    if (bf->scans[f].rc) continue;                      // never entered the pools
+    const uint32_t s0 = s; s += (uint32_t)sc.coded.size();
+    if (file_status[f]) continue;
+    fd.bin_off = ps[s0 < ns ? s0 : 0].bin_off; fd.slice_off = (uint32_t)bsl.size(); fd.nslices = (uint32_t)sc.coded.size();
+    fd.frame_off = (uint32_t)frames.size(); fd.nframes = (uint32_t)sc.rec.frames.size(); fd.block_off = (uint32_t)nblocks;
+    fd.pic_mb_base = (uint32_t)pic_mbs;
+    for (auto& fr : sc.rec.frames) { uint32_t mm = (uint32_t)fr.mb_w * fr.mb_h; if (mm > fd.max_mbs) fd.max_mbs = mm; pic_mbs += mm; }
+    frames.insert(frames.end(), sc.rec.frames.begin(), sc.rec.frames.end());
+    for (uint32_t k = s0; k < s; k++) {
+      AvrBatchSlice bs = {(uint32_t)f, ps[k].file_bin_base, ps[k].file_bin_base + res[k].nbins, (uint32_t)nblocks, (uint32_t)nblocks + res[k].nblocks};
+      blk_cnt[k] = res[k].nblocks; blk_dst[k] = (uint32_t)nblocks;
+      nblocks += res[k].nblocks; emitted += res[k].emitted; nbins += res[k].nbins;
+      bsl.push_back(bs);
+      uint32_t cap = res[k].nbins + 6 * res[k].nblocks + 16;
+      soff.push_back(scratch); scap.push_back(cap); scratch += (cap + 15) & ~15ull;
+    }
+    fd.nblocks = (uint32_t)nblocks - fd.block_off;
+  }
+  b->file_slice_off.push_back((uint32_t)bsl.size());
+  if (emitted >= (1ull << 31) || nblocks + bsl.size() >= (1ull << 31) || pic_mbs >= (1ull << 32)) {
+    avr_set_error("batch too large for one launch (%llu coded symbols); split it", (unsigned long long)emitted); return fail(AVR_E_OVERFLOW);
+  }
+  b->t.bins = nbins; b->t.coded_symbols = emitted; b->scratch_bytes = scratch; b->pic_mbs = pic_mbs;
+  AvrDevBatch& d = b->d;
+  d.nfiles = nfiles; d.nslices = (uint32_t)bsl.size(); d.nblocks = (uint32_t)nblocks; d.nbins = nbins; d.emit_cap = (uint32_t)emitted;
+  d.tab = ctx->d_tab; d.bins = d_bins;
+  int fb = 0; while ((1 << fb) < nfiles) fb++;
+  d.sort_end_bit = 22 + fb;
+  AvrFileDesc* d_fds; AvrBlock* d_blocks; AvrBatchSlice* d_bsl; AvrFrame* d_frames; uint32_t* d_cnt; uint32_t* d_dst;
+  if ((rc = m.alloc(&d_fds, fds.size())) || (rc = m.alloc(&d_blocks, nblocks)) || (rc = m.alloc(&d_bsl, bsl.size())) ||
+      (rc = m.alloc(&d_frames, frames.size())) || (rc = tmp.alloc(&d_cnt, ns)) || (rc = tmp.alloc(&d_dst, ns)) ||
+      (rc = m.alloc(&b->d_scratch_off, soff.size())) || (rc = m.alloc(&b->d_scratch_cap, scap.size())) ||
+      (rc = m.alloc(&d.scratch, scratch)) || (rc = m.alloc(&d.out_len, bsl.size())) || (rc = m.alloc(&d.status, bsl.size())) ||
+      (rc = m.alloc(&d.out_off, bsl.size())) || (rc = m.alloc(&d.out_total, 1)) || (rc = m.alloc(&d.out, scratch)))
+    return fail(rc);
+  d.fds = d_fds; d.blocks = d_blocks; d.bslices = d_bsl; d.frames = d_frames; d.slices = nullptr;
+  d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
+  cudaEventRecord(ctx->ev[0], st);
+  auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };
+  up(d_fds, fds.data(), fds.size() * sizeof(AvrFileDesc)); up(d_bsl, bsl.data(), bsl.size() * sizeof(AvrBatchSlice));
+  up(d_frames, frames.data(), frames.size() * sizeof(AvrFrame)); up(d_cnt, blk_cnt.data(), ns * 4); up(d_dst, blk_dst.data(), ns * 4);
+  up(b->d_scratch_off, soff.data(), soff.size() * 8); up(b->d_scratch_cap, scap.data(), scap.size() * 4);
+  rc = avr_launch_gather_blocks(d_blkpool, d_ps, d_cnt, d_dst, d_blocks, ns, st);
+  cudaEventRecord(ctx->ev[1], st);
+  e = cudaStreamSynchronize(st);
+  if (rc || e != cudaSuccess) { avr_set_error("block gather: %s", cudaGetErrorString(rc ? (cudaError_t)rc : e)); return fail(AVR_E_CUDA); }
+  b->t.h2d_ms += ev_ms(ctx->ev[0], ctx->ev[1]); b->t.h2d_bytes = h2d; b->t.launches = b->create_launches = 2;
+  tmp.release();
+  b->t.host_ms = wall_ms() - t_host0 - b->t.h2d_ms - b->t.parse_ms;
+  files_registry().push_back({b, bf});
+  *out = b;
+  return AVR_OK;
+}
+
+static avr_cbatch_files* files_of(const avr_cbatch* b) {
+  for (auto& p : files_registry()) if (p.first == b) return p.second;
+  return nullptr;
+}
+extern "C" int avr_cbatch_span_count(const avr_cbatch* b, int file, uint32_t* n) {
+  avr_cbatch_files* bf = files_of(b);
+  if (!bf || file < 0 || file >= (int)bf->scans.size() || !n) return AVR_E_ARG;
+  *n = (uint32_t)bf->scans[file].rec.spans.size();
+  return AVR_OK;
+}
+extern "C" int avr_cbatch_span(const avr_cbatch* b, int file, uint32_t i, uint64_t* off, uint32_t* size, int32_t* idx) {
+  avr_cbatch_files* bf = files_of(b);
+  if (!bf || file < 0 || file >= (int)bf->scans.size() || i >= bf->scans[file].rec.spans.size()) return AVR_E_ARG;
+  const avr::SliceSpan& s = bf->scans[file].rec.spans[i];
+  if (off) *off = s.payload_off;
+  if (size) *size = s.size;
+  if (idx) *idx = s.slice_index;
+  return AVR_OK;
+}
+void avr_cbatch_files_release(avr_cbatch* b) {
+  auto& r = files_registry();
+  for (size_t i = 0; i < r.size(); i++) if (r[i].first == b) { delete r[i].second; r.erase(r.begin() + i); return; }
 }

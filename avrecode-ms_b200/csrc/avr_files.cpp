@@ -8,6 +8,7 @@
 #include <atomic>
 #include <string>
 #include <thread>
+#include <chrono>
 #include <vector>
 #include "../../include/avrecode_b200.h"
 #include "avr_api_internal.h"
@@ -114,7 +115,9 @@ void add_timing(avr_timing* acc, const avr_timing& t) {
   acc->h2d_ms += t.h2d_ms; acc->kernel_ms += t.kernel_ms; acc->d2h_ms += t.d2h_ms;
   acc->h2d_bytes += t.h2d_bytes; acc->d2h_bytes += t.d2h_bytes; acc->bins += t.bins;
   acc->coded_symbols += t.coded_symbols; acc->launches += t.launches; acc->coder_launch_ms_x1000 += t.coder_launch_ms_x1000;
+  acc->parse_ms += t.parse_ms; acc->host_ms += t.host_ms;
 }
+double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 bool to_buffer(const std::vector<uint8_t>& v, avr_buffer* b) {
   b->size = v.size();
@@ -129,33 +132,99 @@ bool to_buffer(const std::vector<uint8_t>& v, avr_buffer* b) {
 extern "C" void avr_buffer_free(avr_buffer* b) { if (b) { free(b->data); b->data = nullptr; b->size = 0; } }
 
 // compressor::run (recode.cpp:1122-1132) for n files at once.
+// Phase 1 of avr_compress_files: batches whose CABAC parse runs on the GPU (avr_cbatch_create_files).
+// Marks done[f] for every file it produced a container for; the rest fall to the host recorder.
+static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, const std::vector<int>& ids,
+                                 int host_threads, std::vector<std::vector<uint8_t>>& containers, std::vector<char>& done,
+                                 avr_timing* tt) {
+  if (ids.empty()) return AVR_OK;
+  std::vector<const uint8_t*> fin; std::vector<size_t> flen;
+  for (int f : ids) { fin.push_back(in[f]); flen.push_back(in_len[f]); }
+  std::vector<int> status(ids.size(), 0);
+  avr_cbatch* b = nullptr;
+  int rc = avr_cbatch_create_files(ctx, fin.data(), flen.data(), (int)ids.size(), host_threads, &b, status.data());
+  if (rc == AVR_E_OVERFLOW) {                     // too many coded symbols for one launch: halve
+    if (ids.size() == 1) return AVR_OK;           // left to the host path, which reports the limit
+    std::vector<int> lo(ids.begin(), ids.begin() + ids.size() / 2), hi(ids.begin() + ids.size() / 2, ids.end());
+    rc = compress_device_parse(ctx, in, in_len, lo, host_threads, containers, done, tt);
+    return rc ? rc : compress_device_parse(ctx, in, in_len, hi, host_threads, containers, done, tt);
+  }
+  if (rc == AVR_OK) rc = avr_cbatch_run(b, AVR_MODE_PIPELINE);
+  if (rc == AVR_OK) rc = avr_cbatch_fetch(b);
+  if (rc == AVR_OK) {
+    avr_timing t; avr_cbatch_timing(b, &t); add_timing(tt, t);
+    const double t0 = now_ms();
+    parallel_for((int)ids.size(), host_threads, [&](int k) {
+      if (status[k]) return;
+      const int f = ids[k];
+      std::vector<uint8_t>& o = containers[f];
+      o.reserve(in_len[f] + in_len[f] / 16 + 64);
+      uint32_t nspans = 0; avr_cbatch_span_count(b, k, &nspans);
+      size_t prev_end = 0;
+      for (uint32_t i = 0; i < nspans; i++) {
+        uint64_t off; uint32_t size; int32_t idx;
+        avr_cbatch_span(b, k, i, &off, &size, &idx);
+        if (idx < 0) { put_block_skip(o, size); continue; }
+        put_block_literal(o, in[f] + prev_end, (size_t)off - prev_end);
+        prev_end = (size_t)off + size;
+        const uint8_t* p; uint32_t len;
+        avr_cbatch_payload(b, k, (uint32_t)idx, &p, &len);
+        put_block_cabac(o, size, p, len, (int)(size & 1), size > 1 ? in[f] + prev_end - 1 : nullptr);
+      }
+      put_block_literal(o, in[f] + prev_end, in_len[f] - prev_end);
+      done[f] = 1;
+    });
+    tt->host_ms += now_ms() - t0;
+  }
+  avr_cbatch_destroy(b);
+  return rc;
+}
+
 extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
                                   avr_buffer* out, avr_timing* tacc) {
   if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
   avr_timing tt; memset(&tt, 0, sizeof tt);
+  std::vector<std::vector<uint8_t>> containers((size_t)n);
+  std::vector<char> done((size_t)n, 0);
+  int rc = AVR_OK;
+  // AVR_HOST_PARSE=1 keeps the CABAC parse on the host cores (A/B measurement, bench.py)
+  const char* hp = getenv("AVR_HOST_PARSE");
+  if (!(hp && hp[0] == '1')) {
+    // batches: at most 1024 files and 48 MB of input (~2^29 coded symbols) each
+    for (int i0 = 0; i0 < n && rc == AVR_OK;) {
+      std::vector<int> ids; size_t bytes = 0;
+      for (; i0 < n && ids.size() < 1024 && (ids.empty() || bytes + in_len[i0] <= (48u << 20)); i0++) { ids.push_back(i0); bytes += in_len[i0]; }
+      rc = compress_device_parse(ctx, in, in_len, ids, host_threads, containers, done, &tt);
+    }
+    if (rc != AVR_OK) return rc;
+  }
+  // host recorder for what the device parse left (record capacity exceeded, syntax it rejects)
+  std::vector<int> rest;
+  for (int f = 0; f < n; f++) if (!done[f]) rest.push_back(f);
+  const double t_host0 = now_ms();
   std::vector<avr_record*> recs((size_t)n, nullptr);
   std::vector<int> rec_rc((size_t)n, 0);
-  parallel_for(n, host_threads, [&](int i) {
+  parallel_for((int)rest.size(), host_threads, [&](int k) {
+    const int i = rest[k];
     recs[i] = avr_record_new();
     rec_rc[i] = avr_record_annexb(recs[i], in[i], in_len[i]);
     if (avr_record_view(recs[i])->out_of_domain) rec_rc[i] = AVR_E_UNSUPPORTED;
   });
-  auto cleanup = [&]() { for (auto r : recs) avr_record_free(r); };
-  // batches: at most 1024 files and 2^29 coded symbols each
-  std::vector<std::vector<uint8_t>> containers((size_t)n);
-  int rc = AVR_OK;
-  int i0 = 0;
-  while (i0 < n && rc == AVR_OK) {
+  tt.host_ms += now_ms() - t_host0;
+  auto cleanup = [&]() { for (auto r : recs) if (r) avr_record_free(r); };
+  size_t r0 = 0;
+  while (r0 < rest.size() && rc == AVR_OK) {
     std::vector<int> files;
     uint64_t sym = 0;
-    int i = i0;
-    for (; i < n && files.size() < 1024; i++) {
-      if (rec_rc[i]) continue;
-      uint64_t e = avr_record_view(recs[i])->emitted;
+    size_t i = r0;
+    for (; i < rest.size() && files.size() < 1024; i++) {
+      const int f = rest[i];
+      if (rec_rc[f]) continue;
+      uint64_t e = avr_record_view(recs[f])->emitted;
       if (!files.empty() && sym + e > (1ull << 29)) break;
-      files.push_back(i); sym += e;
+      files.push_back(f); sym += e;
     }
-    i0 = i;
+    r0 = i;
     if (files.empty()) continue;
     std::vector<const avr_record*> br;
     for (int f : files) br.push_back(recs[f]);
@@ -189,7 +258,7 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
   for (int f = 0; f < n; f++) {
     // streams the device path does not cover (CAVLC, B/field/MBAFF, 4:2:2+, I_PCM, repeated frame_num)
     // are stored whole as one literal block: a valid container that restores the input.
-    if (rec_rc[f]) { containers[f].clear(); put_block_literal(containers[f], in[f], in_len[f]); }
+    if (!done[f] && rec_rc[f]) { containers[f].clear(); put_block_literal(containers[f], in[f], in_len[f]); }
     if (!to_buffer(containers[f], &out[f])) { cleanup(); return AVR_E_NOMEM; }
   }
   cleanup();

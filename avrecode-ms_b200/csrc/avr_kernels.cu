@@ -9,6 +9,7 @@
 #include "avr_kernels.h"
 #include "avr_pipeline.h"
 #include "avr_decode.h"
+#include "avr_parse.h"
 
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fds, int nfiles, const uint16_t* bins,
@@ -73,6 +74,30 @@ __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
       if (rc) s_failed = 1;
     }
     __syncthreads();
+  }
+}
+
+// Compress-side parse on the device (avr_parse.h): one warp per coded slice, lane 0 walks the slice,
+// all lanes initialise the CABAC states and tables.
+__global__ void __launch_bounds__(32) avr_k_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool,
+                                                  AvrBlock* blk_pool, avr::MbInfo* row_pool, const uint64_t* row_off,
+                                                  const AvrTables* tab, AvrParseResult* res) {
+  const uint32_t s = blockIdx.x, lane = threadIdx.x;
+  if (s >= n) return;
+  const AvrParseSlice& p = ps[s];
+  for (uint32_t i = lane; i < 256; i += 32) g_par.range_lps[i] = tab->hot.range_lps[i];
+  for (uint32_t i = lane; i < 64; i += 32) g_par.trans_lps[i] = tab->hot.trans_lps[i];
+  avr_cabac_init_states(g_par.st, tab, p.sp.slice_type == avr::SLICE_I, p.sp.cabac_init_idc, p.sp.slice_qp, (int)lane, 32);
+  __syncwarp();
+  if (lane == 0) avr_parse_slice(p, raw, bins_pool, blk_pool, row_pool + row_off[s], &res[s]);
+}
+// capacity block pool -> dense block array
+__global__ void __launch_bounds__(128) avr_k_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count,
+                                                           const uint32_t* dst_off, AvrBlock* dst, uint32_t n) {
+  for (uint32_t s = blockIdx.x; s < n; s += gridDim.x) {
+    const uint4* src = reinterpret_cast<const uint4*>(pool + ps[s].blk_off);
+    uint4* d = reinterpret_cast<uint4*>(dst + dst_off[s]);
+    for (uint32_t i = threadIdx.x; i < count[s]; i += blockDim.x) d[i] = src[i];
   }
 }
 
@@ -248,5 +273,18 @@ int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* lau
   avr_k_code<<<(b.nslices + 31) / 32, 32, 0, st>>>(a); nl++;
   if (coder_end) cudaEventRecord(coder_end, st);
   if (launches) *launches = nl;
+  return (int)cudaGetLastError();
+}
+
+int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
+                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, cudaStream_t st) {
+  if (n == 0) return 0;
+  avr_k_parse<<<n, 32, 0, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res);
+  return (int)cudaGetLastError();
+}
+int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,
+                             AvrBlock* dst, uint32_t n, cudaStream_t st) {
+  if (n == 0) return 0;
+  avr_k_gather_blocks<<<n < 148u * 16u ? n : 148u * 16u, 128, 0, st>>>(pool, ps, count, dst_off, dst, n);
   return (int)cudaGetLastError();
 }

@@ -71,6 +71,36 @@ int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(co
   return AVR_OK;
 }
 
+// Host half of the device-side parse (avr_parse.h): everything record_annexb does EXCEPT the CABAC
+// decode -- NAL scan, headers, update_frame_spec bookkeeping, the block-finder decision.
+int scan_annexb(const uint8_t* data, size_t n, FileRecord* out, std::vector<ScanSlice>* coded) {
+  Recorder rec(out, nullptr);
+  size_t prev_coded_end = 0;
+  int rc = scan_annexb_slices(data, n, [&](const SliceLoc& loc) -> int {
+    const SliceHeaderInfo& sh = loc.sh;
+    if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);
+    bool found = false;
+    size_t found_at = 0;
+    if (loc.size >= 8 && loc.raw_off >= prev_coded_end) {
+      size_t hay_end = loc.raw_off + loc.size <= n ? loc.raw_off + loc.size : n;
+      const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, loc.payload, loc.size);
+      if (m) { found = true; found_at = (size_t)((const uint8_t*)m - data); }
+    }
+    rec.slice_begin(found, found ? found_at : loc.raw_off, (uint32_t)loc.size, sh.sp);
+    if (!found) return 0;
+    prev_coded_end = found_at + loc.size;
+    ScanSlice s;
+    s.raw_off = found_at; s.size = (uint32_t)loc.size; s.frame = rec.cur_frame(); s.sp = sh.sp;
+    s.slice_index = (int32_t)out->slices.size() - 1;
+    for (int k = 0; k < 4; k++) s.tail[k] = loc.size + k < loc.payload_avail ? loc.payload[loc.size + k] : 0;
+    coded->push_back(s);
+    rec.slice_end();
+    return 0;
+  });
+  out->error = rc;
+  return rc;
+}
+
 int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
   Recorder rec(out, trace);
   std::vector<MbInfo> row;

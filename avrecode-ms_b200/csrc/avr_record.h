@@ -148,6 +148,17 @@ struct SliceLoc {
 // Returns AVR_OK, the callback's non-zero result, or AVR_E_UNSUPPORTED (CAVLC / B / field / FMO / 4:2:2+).
 int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice);
 
+// One coded slice found by scan_annexb: what the device-side parse (avr_parse.h) needs.
+struct ScanSlice {
+  uint64_t raw_off;        // file offset of the first CABAC byte (the block-finder's match)
+  uint32_t size;
+  uint8_t tail[4];         // unescaped bytes after the payload that libavcodec's CABAC reader may peek at
+  uint32_t frame;          // picture (flip) index
+  int32_t slice_index;     // index among the file's coded slices
+  SliceParams sp;
+};
+int scan_annexb(const uint8_t* data, size_t n, FileRecord* out, std::vector<ScanSlice>* coded);
+
 // Native front end: parse an Annex-B H.264 byte stream without libavcodec.
 // Returns AVR_OK, AVR_E_UNSUPPORTED (stream uses syntax outside h264_syntax.h) or AVR_E_CORRUPT.
 int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace = nullptr);

@@ -74,6 +74,8 @@ typedef struct avr_timing {
   uint64_t coded_symbols;                 /* symbols through the range coder (EOB bins excluded, nnz bits included) */
   uint32_t launches;                      /* kernels launched by the run */
   uint32_t coder_launch_ms_x1000;         /* duration of the dominant kernel (range-coder pass / chain kernel), microseconds */
+  double parse_ms;                        /* device-side parse kernel (avr_cbatch_create_files), CUDA events */
+  double host_ms;                         /* host wall time inside the call(s): scan, staging, framing */
 } avr_timing;
 
 /* ---- context ---------------------------------------------------------------------------- */
@@ -107,6 +109,15 @@ int avr_record_span(const avr_record* r, uint32_t i, uint64_t* payload_off, uint
 #define AVR_MODE_PIPELINE 0   /* slice-parallel pipeline (product path) */
 #define AVR_MODE_CHAIN 1      /* one sequential chain per file (on-device cross-check) */
 int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs, int nfiles, avr_cbatch** out);  /* H2D */
+/* Same, from raw Annex-B files: the host only scans NALs/headers; the CABAC decode + slice_data() walk that
+ * produces the records runs on the GPU (one warp per slice).  file_status[i] != AVR_OK marks a file the device
+ * parse does not cover (unsupported syntax, record capacity exceeded): it is left out of the batch and the
+ * caller decides (avr_compress_files falls back to the host recorder, then to a literal block). */
+int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* files, const size_t* lens, int nfiles,
+                            int host_threads, avr_cbatch** out, int* file_status);
+/* spans (coded + skipped slices, in stream order) of file `file` of a batch made by avr_cbatch_create_files */
+int avr_cbatch_span_count(const avr_cbatch* b, int file, uint32_t* nspans);
+int avr_cbatch_span(const avr_cbatch* b, int file, uint32_t i, uint64_t* payload_off, uint32_t* size, int32_t* slice_index);
 int avr_cbatch_run(avr_cbatch* b, int mode);                                                           /* kernels only */
 int avr_cbatch_fetch(avr_cbatch* b);                                                                   /* D2H */
 int avr_cbatch_payload(const avr_cbatch* b, int file, uint32_t slice, const uint8_t** data, uint32_t* len);

@@ -14,6 +14,7 @@
 #include "../avrecode-ms_b200/csrc/avr_host_tables.h"
 #include "../avrecode-ms_b200/csrc/avr_pipeline.h"
 #include "../avrecode-ms_b200/csrc/avr_decode.h"
+#include "../avrecode-ms_b200/csrc/avr_parse.h"
 #include <algorithm>
 
 static bool read_file(const char* fn, std::vector<uint8_t>* out) {
@@ -194,6 +195,38 @@ static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRec
   return bad;
 }
 
+// device-side parse body (avr_parse.h) on the host, slice by slice, against the host recorder
+static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& want, const AvrTables& tab) {
+  avr::FileRecord scan;
+  std::vector<avr::ScanSlice> coded;
+  int rc = avr::scan_annexb(data.data(), data.size(), &scan, &coded);
+  if (rc) { printf("scan rc=%d\n", rc); return 1; }
+  std::vector<uint16_t> bins; std::vector<AvrBlock> blocks;
+  memcpy(g_par.range_lps, tab.hot.range_lps, 256); memcpy(g_par.trans_lps, tab.hot.trans_lps, 64);
+  std::vector<uint8_t> raw(data); raw.resize(raw.size() + 16);
+  uint64_t emitted = 0;
+  for (const avr::ScanSlice& c : coded) {
+    AvrParseSlice ps;
+    memset(&ps, 0, sizeof ps);
+    ps.raw_off = c.raw_off; ps.size = c.size; memcpy(ps.tail, c.tail, 4);
+    ps.bin_cap = 24 * c.size + 2048; ps.blk_cap = ps.bin_cap / 4; ps.file_bin_base = (uint32_t)bins.size();
+    ps.frame = c.frame; ps.sp = c.sp;
+    std::vector<uint16_t> b(ps.bin_cap); std::vector<AvrBlock> k(ps.blk_cap); std::vector<avr::MbInfo> row((size_t)c.sp.mb_w);
+    avr_cabac_init_states(g_par.st, &tab, c.sp.slice_type == avr::SLICE_I, c.sp.cabac_init_idc, c.sp.slice_qp, 0, 1);
+    AvrParseResult res;
+    avr_parse_slice(ps, raw.data(), b.data(), k.data(), row.data(), &res);
+    if (res.status) { printf("slice status %d\n", res.status); return 1; }
+    bins.insert(bins.end(), b.begin(), b.begin() + res.nbins);
+    blocks.insert(blocks.end(), k.begin(), k.begin() + res.nblocks);
+    emitted += res.emitted;
+  }
+  bool ok = bins == want.bins && blocks.size() == want.blocks.size() && emitted == want.emitted &&
+            scan.spans.size() == want.spans.size() && scan.frames.size() == want.frames.size();
+  for (size_t i = 0; ok && i < blocks.size(); i++) ok = !memcmp(&blocks[i], &want.blocks[i], sizeof(AvrBlock));
+  printf("%s bins=%zu blocks=%zu emitted=%llu\n", ok ? "OK" : "FAIL", bins.size(), blocks.size(), (unsigned long long)emitted);
+  return ok ? 0 : 1;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) { fprintf(stderr, "usage: %s chain|pipeline|roundtrip <clip>\n", argv[0]); return 2; }
   std::string cmd = argv[1];
@@ -221,6 +254,7 @@ int main(int argc, char** argv) {
     if (compress_pipeline(recs, tab, &all)) return 1;
     c = all.back();
   }
+  if (cmd == "parse") return parse_check(data, rec, tab);
   if (cmd == "roundtrip") return decompress_check(data, rec, tab, c) ? 1 : 0;
   for (auto& p : c.payloads) print_hex("P ", p.data(), p.size());
   return 0;

@@ -45,6 +45,36 @@ def test_container_is_byte_identical_to_reference(ctx, name):
     assert comp[0] == open(os.path.join(GOLDEN, name + ".avrec"), "rb").read()
 
 
+def test_device_parse_batch_matches_reference_golden(ctx):
+    """raw files in, CABAC parse on the GPU (avr_k_parse): payloads == the reference's, spans == host recorder's"""
+    import avr_ctypes as A
+    datas = [open(os.path.join(GOLDEN, n + ".h264"), "rb").read() for n in GOLDEN_NAMES]
+    b = A.CBatch(ctx, files=datas)
+    assert b.file_status == [0] * len(datas)
+    b.run(A.MODE_PIPELINE)
+    b.fetch()
+    got = b.payloads()
+    for n, g in zip(GOLDEN_NAMES, got):
+        assert g == golden_payloads(n), n
+    t = b.timing()
+    assert t["parse_ms"] > 0 and t["launches"] > 2
+    b.close()
+
+
+def test_host_parse_path_gives_the_same_containers(ctx, tmpdir_path, monkeypatch):
+    """the fallback (host recorder) and the device parse write identical containers"""
+    import avr_ctypes as A
+    datas = [gen_clip(os.path.join(tmpdir_path, f"h{i}.h264"), seed=70 + i, mb_w=9 + i, mb_h=5 + i, frames=4,
+                      slices_per_frame=1 + i, transform_8x8=i & 1, p_skip=120 + 40 * i) for i in range(3)]
+    dev, td = A.compress_files(ctx, datas)
+    monkeypatch.setenv("AVR_HOST_PARSE", "1")
+    host, th = A.compress_files(ctx, datas)
+    monkeypatch.delenv("AVR_HOST_PARSE")
+    assert dev == host
+    assert td["parse_ms"] > 0 and th["parse_ms"] == 0
+    assert td["coded_symbols"] == th["coded_symbols"]
+
+
 def test_decompress_reference_containers(ctx):
     """our decompressor restores the input from containers written by the REFERENCE compressor"""
     import avr_ctypes as A

@@ -29,6 +29,13 @@ def test_decompress_body_restores_original_cabac_bytes(name):
     assert rc == 0 and out.startswith(b"OK"), out + err
 
 
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_device_parse_body_emits_the_host_recorders_records(name):
+    """avr_parse.h (compress-side CABAC parse, one slice per warp) == avr_record.cpp on bins, blocks, counts"""
+    rc, out, err = run([EMUL, "parse", os.path.join(GOLDEN, name + ".h264")])
+    assert rc == 0 and out.startswith(b"OK"), out + err
+
+
 def test_pipeline_batch_of_files_keeps_models_separate():
     """the estimator state is per file (recode.cpp:1314): other files in the batch must not leak in"""
     clips = [os.path.join(GOLDEN, n + ".h264") for n in ("dct8x8", "skippy_idr", "ip_basic")]
@@ -54,5 +61,6 @@ def test_bodies_match_oracle_on_fresh_clips(params, tmpdir_path):
         rc, out, err = run([EMUL, mode, clip])
         assert rc == 0, err
         assert hex_payloads(out) == want, mode
-    rc, out, err = run([EMUL, "roundtrip", clip])
-    assert rc == 0 and out.startswith(b"OK"), out + err
+    for cmd in ("roundtrip", "parse"):
+        rc, out, err = run([EMUL, cmd, clip])
+        assert rc == 0 and out.startswith(b"OK"), out + err
