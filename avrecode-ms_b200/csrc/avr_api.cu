@@ -24,11 +24,33 @@ extern "C" int avr_version(void) { return 100; }
 
 #define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { avr_set_error("%s: %s", #x, cudaGetErrorString(e_)); return AVR_E_CUDA; } } while (0)
 
+// Device blocks released by a batch stay with the context and are handed to the next batch: cudaMalloc /
+// cudaFree of multi-GB buffers cost 50-200 ms per batch, more than some of the kernels.  Everything runs on
+// the context's one stream and batches synchronise before they release, so reuse needs no extra ordering.
+struct AvrArena {
+  std::vector<std::pair<size_t, void*>> free_blocks;
+  size_t cached = 0;
+  void* take(size_t n, size_t* got) {
+    size_t best = (size_t)-1, bi = 0;
+    for (size_t i = 0; i < free_blocks.size(); i++) {
+      const size_t sz = free_blocks[i].first;
+      if (sz >= n && sz <= 2 * n + (1u << 20) && sz < best) { best = sz; bi = i; }
+    }
+    if (best == (size_t)-1) return nullptr;
+    void* p = free_blocks[bi].second;
+    cached -= best; *got = best;
+    free_blocks.erase(free_blocks.begin() + bi);
+    return p;
+  }
+  void give(void* p, size_t n) { free_blocks.push_back({n, p}); cached += n; }
+  void flush() { for (auto& b : free_blocks) cudaFree(b.second); free_blocks.clear(); cached = 0; }
+};
 struct avr_context {
   int device;
   cudaStream_t stream;
   AvrTables* d_tab;
   cudaEvent_t ev[4];
+  AvrArena arena;
 };
 
 extern "C" int avr_context_create(int device, avr_context** out) {
@@ -54,6 +76,7 @@ extern "C" int avr_context_create(int device, avr_context** out) {
 extern "C" void avr_context_destroy(avr_context* c) {
   if (!c) return;
   cudaSetDevice(c->device);
+  c->arena.flush();
   cudaFree(c->d_tab);
   for (auto& e : c->ev) cudaEventDestroy(e);
   cudaStreamDestroy(c->stream);
@@ -129,18 +152,27 @@ extern "C" int avr_record_span(const avr_record* r, uint32_t i, uint64_t* off, u
 
 // ---- device memory helper ---------------------------------------------------------------------
 struct DevMem {
-  std::vector<void*> ptrs;
+  std::vector<std::pair<size_t, void*>> ptrs;
   size_t bytes = 0;
+  AvrArena* arena = nullptr;             // the owning context's block cache (set by the batch constructors)
   template <class T> int alloc(T** p, size_t count) {
     *p = nullptr;
     size_t n = (count ? count : 1) * sizeof(T) + 64;
-    void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, n);
-    if (e != cudaSuccess) { avr_set_error("cudaMalloc(%zu): %s", n, cudaGetErrorString(e)); return AVR_E_NOMEM; }
-    ptrs.push_back(q); bytes += n; *p = (T*)q;
+    n = n >= (1u << 20) ? (n + (2u << 20) - 1) & ~(size_t)((2u << 20) - 1) : (n + 511) & ~(size_t)511;
+    size_t got = n;
+    void* q = arena ? arena->take(n, &got) : nullptr;
+    if (!q) {
+      cudaError_t e = cudaMalloc(&q, n);
+      if (e != cudaSuccess && arena && arena->cached) { cudaGetLastError(); arena->flush(); e = cudaMalloc(&q, n); }
+      if (e != cudaSuccess) { cudaGetLastError(); avr_set_error("cudaMalloc(%zu): %s", n, cudaGetErrorString(e)); return AVR_E_NOMEM; }
+    }
+    ptrs.push_back({got, q}); bytes += got; *p = (T*)q;
     return AVR_OK;
   }
-  void release() { for (void* p : ptrs) cudaFree(p); ptrs.clear(); bytes = 0; }
+  void release() {
+    for (auto& b : ptrs) { if (arena) arena->give(b.second, b.first); else cudaFree(b.second); }
+    ptrs.clear(); bytes = 0;
+  }
 };
 #define TRY(x) do { int r_ = (x); if (r_ != AVR_OK) return r_; } while (0)
 
@@ -168,7 +200,7 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
   if (nfiles > 1024) { avr_set_error("at most 1024 files per batch (sort key has 10 file bits)"); return AVR_E_ARG; }
   CU(cudaSetDevice(ctx->device));
   avr_cbatch* b = new avr_cbatch();
-  b->ctx = ctx;
+  b->ctx = ctx; b->mem.arena = &ctx->arena;
   memset(&b->d, 0, sizeof b->d);
   memset(&b->t, 0, sizeof b->t);
   std::vector<AvrFileDesc> fds((size_t)nfiles);
@@ -366,7 +398,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   if (!ctx || (!slices && nfiles) || !per_file || nfiles < 0 || !out) return AVR_E_ARG;
   CU(cudaSetDevice(ctx->device));
   avr_dbatch* b = new avr_dbatch();
-  b->ctx = ctx;
+  b->ctx = ctx; b->mem.arena = &ctx->arena;
   memset(&b->d, 0, sizeof b->d);
   memset(&b->t, 0, sizeof b->t);
   std::vector<AvrFileDesc> fds((size_t)nfiles);
@@ -401,6 +433,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   AvrDevDBatch& d = b->d;
   DevMem& m = b->mem;
   d.nfiles = nfiles; d.nslices = (uint32_t)ds.size(); d.tab = ctx->d_tab;
+  avr_trace(nullptr);
   AvrFileDesc* d_fds; AvrDecSlice* d_ds; uint8_t* d_pay;
   int rc;
   auto fail = [&](int r) { m.release(); delete b; return r; };
@@ -409,6 +442,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
       (rc = m.alloc(&d.row_pool, (size_t)chain_mbs)) || (rc = m.alloc(&d.out, outb)) || (rc = m.alloc(&d.out_len, ds.size())) ||
       (rc = m.alloc(&d.out_bins, ds.size())) || (rc = m.alloc(&d.status, ds.size())))
     return fail(rc);
+  avr_trace("dc: alloc");
   d.fds = d_fds; d.slices = d_ds; d.payloads = d_pay;
   cudaStream_t st = ctx->stream;
   cudaEventRecord(ctx->ev[0], st);
@@ -420,6 +454,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   cudaEventRecord(ctx->ev[1], st);
   cudaError_t e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) { avr_set_error("upload: %s", cudaGetErrorString(e)); return fail(AVR_E_CUDA); }
+  avr_trace("dc: upload");
   b->t.h2d_ms = ev_ms(ctx->ev[0], ctx->ev[1]);
   b->t.h2d_bytes = h2d;
   *out = b;
@@ -524,6 +559,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   if (nfiles > 1024) { avr_set_error("at most 1024 files per batch (sort key has 10 file bits)"); return AVR_E_ARG; }
   CU(cudaSetDevice(ctx->device));
   const double t_host0 = wall_ms();
+  avr_trace(nullptr);
   avr_cbatch_files* bf = new avr_cbatch_files();
   bf->scans.resize((size_t)nfiles);
   par_for(nfiles, host_threads, [&](int f) {
@@ -531,6 +567,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
     sc.rc = avr::scan_annexb(files[f], lens[f], &sc.rec, &sc.coded);
     if (!sc.rc && sc.rec.out_of_domain) sc.rc = AVR_E_UNSUPPORTED;
   });
+  avr_trace("cf: host scan");
   // layout of the pools
   std::vector<AvrParseSlice> ps; std::vector<uint64_t> row_off; std::vector<int> ps_file;
   std::vector<uint64_t> raw_base((size_t)nfiles, 0);
@@ -544,16 +581,16 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
       p.raw_off = raw_base[f] + c.raw_off; p.size = c.size; memcpy(p.tail, c.tail, 4);
       // records per CABAC byte: ~11 bins typical; skip runs cost ~2 bins per macroblock and almost no bytes
       const uint32_t mbs = (uint32_t)c.sp.mb_w * (uint32_t)c.sp.mb_h;
-      p.bin_cap = 24u * c.size + 4u * (mbs > (uint32_t)c.sp.first_mb ? mbs - (uint32_t)c.sp.first_mb : 0u) + 2048u; p.blk_cap = p.bin_cap / 4;
+      p.bin_cap = 24u * c.size + 4u * (mbs > (uint32_t)c.sp.first_mb ? mbs - (uint32_t)c.sp.first_mb : 0u) + 2048u; p.blk_cap = p.bin_cap / 6;
       p.bin_off = bin_pool; bin_pool += p.bin_cap; p.blk_off = blk_pool; blk_pool += p.blk_cap;
       p.frame = c.frame; p.sp = c.sp;
       ps.push_back(p); ps_file.push_back(f); row_off.push_back(rows); rows += (uint64_t)c.sp.mb_w;
     }
   }
   avr_cbatch* b = new avr_cbatch();
-  b->ctx = ctx; memset(&b->d, 0, sizeof b->d); memset(&b->t, 0, sizeof b->t);
+  b->ctx = ctx; b->mem.arena = &ctx->arena; memset(&b->d, 0, sizeof b->d); memset(&b->t, 0, sizeof b->t);
   DevMem& m = b->mem;
-  DevMem tmp;   // freed before returning
+  DevMem tmp; tmp.arena = &ctx->arena;   // returned to the context before this call ends
   auto fail = [&](int r) { tmp.release(); m.release(); delete b; delete bf; return r; };
   const uint32_t ns = (uint32_t)ps.size();
   uint8_t* d_raw; uint16_t* d_bins; AvrBlock* d_blkpool; avr::MbInfo* d_rows; uint64_t* d_row_off; AvrParseSlice* d_ps; AvrParseResult* d_res;
@@ -561,6 +598,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   if ((rc = tmp.alloc(&d_raw, raw_bytes + 64)) || (rc = m.alloc(&d_bins, bin_pool)) || (rc = tmp.alloc(&d_blkpool, blk_pool)) ||
       (rc = tmp.alloc(&d_rows, rows)) || (rc = tmp.alloc(&d_row_off, ns)) || (rc = tmp.alloc(&d_ps, ns)) || (rc = tmp.alloc(&d_res, ns)))
     return fail(rc);
+  avr_trace("cf: pool alloc");
   cudaStream_t st = ctx->stream;
   // file-local bin numbering = position in the file's region of the bins pool
   {
@@ -584,6 +622,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   cudaMemcpyAsync(res.data(), d_res, ns * sizeof(AvrParseResult), cudaMemcpyDeviceToHost, st);
   cudaError_t e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) { avr_set_error("parse kernel: %s", cudaGetErrorString(e)); return fail(AVR_E_CUDA); }
+  avr_trace("cf: upload+parse+results");
   b->t.h2d_ms = ev_ms(ctx->ev[0], ctx->ev[1]); b->t.parse_ms = ev_ms(ctx->ev[1], ctx->ev[2]); b->t.launches = 1;
   // files with a failed slice drop out of the batch
   for (uint32_t s = 0; s < ns; s++) if (res[s].status && !file_status[ps_file[s]]) file_status[ps_file[s]] = res[s].status;
@@ -632,6 +671,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
       (rc = m.alloc(&d.scratch, scratch)) || (rc = m.alloc(&d.out_len, bsl.size())) || (rc = m.alloc(&d.status, bsl.size())) ||
       (rc = m.alloc(&d.out_off, bsl.size())) || (rc = m.alloc(&d.out_total, 1)) || (rc = m.alloc(&d.out, scratch)))
     return fail(rc);
+  avr_trace("cf: layout+alloc2");
   d.fds = d_fds; d.blocks = d_blocks; d.bslices = d_bsl; d.frames = d_frames; d.slices = nullptr;
   d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
   cudaEventRecord(ctx->ev[0], st);
@@ -644,8 +684,10 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   e = cudaStreamSynchronize(st);
   if (rc || e != cudaSuccess) { avr_set_error("block gather: %s", cudaGetErrorString(rc ? (cudaError_t)rc : e)); return fail(AVR_E_CUDA); }
   b->t.h2d_ms += ev_ms(ctx->ev[0], ctx->ev[1]); b->t.h2d_bytes = h2d; b->t.launches = b->create_launches = 2;
+  avr_trace("cf: gather");
   tmp.release();
   b->t.host_ms = wall_ms() - t_host0 - b->t.h2d_ms - b->t.parse_ms;
+  avr_trace("cf: free tmp");
   files_registry().push_back({b, bf});
   *out = b;
   return AVR_OK;

@@ -7,3 +7,5 @@ void avr_set_error(const char* fmt, ...);
 const avr::FileRecord* avr_record_view(const avr_record* r);
 avr::FileRecord* avr_record_mut(avr_record* r);
 uint32_t avr_span_flip(const avr::FileRecord& rec, uint32_t span_index);
+// AVR_TRACE=1: stage wall times on stderr (diagnostics for the e2e path; off by default)
+void avr_trace(const char* what);

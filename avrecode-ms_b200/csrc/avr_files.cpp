@@ -117,6 +117,16 @@ void add_timing(avr_timing* acc, const avr_timing& t) {
   acc->coded_symbols += t.coded_symbols; acc->launches += t.launches; acc->coder_launch_ms_x1000 += t.coder_launch_ms_x1000;
   acc->parse_ms += t.parse_ms; acc->host_ms += t.host_ms;
 }
+}  // namespace
+void avr_trace(const char* what) {
+  static const bool on = [] { const char* e = getenv("AVR_TRACE"); return e && e[0] == '1'; }();
+  static thread_local double last = 0;
+  if (!on) return;
+  const double t = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  if (what) fprintf(stderr, "[avr] %-28s %9.2f ms\n", what, last ? t - last : 0.0);
+  last = t;
+}
+namespace {
 double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 bool to_buffer(const std::vector<uint8_t>& v, avr_buffer* b) {
@@ -149,8 +159,11 @@ static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, con
     rc = compress_device_parse(ctx, in, in_len, lo, host_threads, containers, done, tt);
     return rc ? rc : compress_device_parse(ctx, in, in_len, hi, host_threads, containers, done, tt);
   }
+  avr_trace(nullptr);
   if (rc == AVR_OK) rc = avr_cbatch_run(b, AVR_MODE_PIPELINE);
+  avr_trace("c: run");
   if (rc == AVR_OK) rc = avr_cbatch_fetch(b);
+  avr_trace("c: fetch");
   if (rc == AVR_OK) {
     avr_timing t; avr_cbatch_timing(b, &t); add_timing(tt, t);
     const double t0 = now_ms();
@@ -175,8 +188,10 @@ static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, con
       done[f] = 1;
     });
     tt->host_ms += now_ms() - t0;
+    avr_trace("c: containers");
   }
   avr_cbatch_destroy(b);
+  avr_trace("c: destroy");
   return rc;
 }
 
@@ -184,16 +199,18 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
                                   avr_buffer* out, avr_timing* tacc) {
   if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
   avr_timing tt; memset(&tt, 0, sizeof tt);
+  const double t_call0 = now_ms();
   std::vector<std::vector<uint8_t>> containers((size_t)n);
   std::vector<char> done((size_t)n, 0);
   int rc = AVR_OK;
   // AVR_HOST_PARSE=1 keeps the CABAC parse on the host cores (A/B measurement, bench.py)
   const char* hp = getenv("AVR_HOST_PARSE");
   if (!(hp && hp[0] == '1')) {
-    // batches: at most 1024 files and 48 MB of input (~2^29 coded symbols) each
+    // batches: at most 1024 files and 192 MB of input each (~8.4 coded symbols per input byte on High-profile
+    // streams, the launch limit is 2^31); a batch that still exceeds the limit is halved (AVR_E_OVERFLOW)
     for (int i0 = 0; i0 < n && rc == AVR_OK;) {
       std::vector<int> ids; size_t bytes = 0;
-      for (; i0 < n && ids.size() < 1024 && (ids.empty() || bytes + in_len[i0] <= (48u << 20)); i0++) { ids.push_back(i0); bytes += in_len[i0]; }
+      for (; i0 < n && ids.size() < 1024 && (ids.empty() || bytes + in_len[i0] <= (192u << 20)); i0++) { ids.push_back(i0); bytes += in_len[i0]; }
       rc = compress_device_parse(ctx, in, in_len, ids, host_threads, containers, done, &tt);
     }
     if (rc != AVR_OK) return rc;
@@ -221,7 +238,7 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
       const int f = rest[i];
       if (rec_rc[f]) continue;
       uint64_t e = avr_record_view(recs[f])->emitted;
-      if (!files.empty() && sym + e > (1ull << 29)) break;
+      if (!files.empty() && sym + e > 1900000000ull) break;
       files.push_back(f); sym += e;
     }
     r0 = i;
@@ -255,13 +272,18 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
     avr_cbatch_destroy(b);
   }
   if (rc != AVR_OK) { cleanup(); return rc; }
-  for (int f = 0; f < n; f++) {
+  avr_trace(nullptr);
+  std::atomic<int> nomem(0);
+  parallel_for(n, host_threads, [&](int f) {
     // streams the device path does not cover (CAVLC, B/field/MBAFF, 4:2:2+, I_PCM, repeated frame_num)
     // are stored whole as one literal block: a valid container that restores the input.
     if (!done[f] && rec_rc[f]) { containers[f].clear(); put_block_literal(containers[f], in[f], in_len[f]); }
-    if (!to_buffer(containers[f], &out[f])) { cleanup(); return AVR_E_NOMEM; }
-  }
+    if (!to_buffer(containers[f], &out[f])) nomem = 1;
+  });
   cleanup();
+  avr_trace("c: to_buffer");
+  if (nomem) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return AVR_E_NOMEM; }
+  tt.host_ms = now_ms() - t_call0 - (tt.h2d_ms + tt.parse_ms + tt.kernel_ms + tt.d2h_ms);   // everything not on the device clock
   if (tacc) *tacc = tt;
   return AVR_OK;
 }
@@ -281,6 +303,8 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
                                     avr_buffer* out, avr_timing* tacc) {
   if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
   avr_timing tt; memset(&tt, 0, sizeof tt);
+  const double t_call0 = now_ms();
+  avr_trace(nullptr);
   std::vector<DFile> files((size_t)n);
   parallel_for(n, host_threads, [&](int f) {
     DFile& d = files[f];
@@ -338,6 +362,7 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
   for (int f = 0; f < n; f++)
     if (files[f].rc) { avr_set_error("container %d: invalid (%d)", f, files[f].rc); return files[f].rc; }
 
+  avr_trace("d: containers+scan");
   std::vector<std::vector<std::vector<uint8_t>>> decoded((size_t)n);   // [file][slice] bytes after the padding patch
   for (int f = 0; f < n; f++) decoded[f].resize(files[f].slices.size());
   int rc = AVR_OK;
@@ -356,14 +381,20 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
     f0 = f;
     if (ids.empty()) continue;
     avr_dbatch* b = nullptr;
+    avr_trace("d: batch lists");
     rc = avr_dbatch_create(ctx, sl.data(), per.data(), (int)ids.size(), &b);
+    avr_trace(nullptr);
     if (rc == AVR_OK) rc = avr_dbatch_run(b);
+    avr_trace("d: run");
     if (rc == AVR_OK) rc = avr_dbatch_fetch(b);
+    avr_trace("d: fetch");
     if (rc == AVR_OK) {
       avr_timing t; avr_dbatch_timing(b, &t); add_timing(&tt, t);
-      uint32_t g = 0;
-      for (size_t k = 0; k < ids.size(); k++) {
+      std::vector<uint32_t> first(ids.size(), 0);
+      for (size_t k = 1; k < ids.size(); k++) first[k] = first[k - 1] + per[k - 1];
+      parallel_for((int)ids.size(), host_threads, [&](int k) {
         DFile& d = files[ids[k]];
+        uint32_t g = first[k];
         for (size_t s = 0; s < d.slices.size(); s++, g++) {
           const uint8_t* p; uint32_t len;
           avr_dbatch_slice(b, g, &p, &len, nullptr);
@@ -375,26 +406,36 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
             else if (!o.empty()) o.back() = blk.last[0];
           }
         }
-      }
+      });
+      avr_trace("d: patch copies");
     }
     avr_dbatch_destroy(b);
+    avr_trace("d: destroy");
   }
   if (rc != AVR_OK) return rc;
-  for (int f = 0; f < n; f++) {
+  std::atomic<int> nomem(0);
+  parallel_for(n, host_threads, [&](int f) {
     DFile& d = files[f];
-    std::vector<uint8_t> o;
-    o.reserve(d.surrogate.size() + 16);
-    size_t s = 0;
     std::vector<int> blk_slice(d.blocks.size(), -1);
     for (size_t k = 0; k < d.slice_block.size(); k++) blk_slice[d.slice_block[k]] = (int)k;
+    size_t total = 0;
     for (size_t i = 0; i < d.blocks.size(); i++) {
       const Block& b = d.blocks[i];
-      if (b.has_literal) o.insert(o.end(), b.literal, b.literal + b.literal_len);
-      else if (b.has_cabac) { const auto& v = decoded[f][blk_slice[i]]; o.insert(o.end(), v.begin(), v.end()); }
+      total += b.has_literal ? b.literal_len : b.has_cabac ? decoded[f][blk_slice[i]].size() : 0;
     }
-    (void)s;
-    if (!to_buffer(o, &out[f])) return AVR_E_NOMEM;
-  }
+    out[f].size = total;
+    out[f].data = (uint8_t*)malloc(total ? total : 1);
+    if (!out[f].data) { nomem = 1; return; }
+    uint8_t* o = out[f].data;
+    for (size_t i = 0; i < d.blocks.size(); i++) {
+      const Block& b = d.blocks[i];
+      if (b.has_literal) { if (b.literal_len) memcpy(o, b.literal, b.literal_len); o += b.literal_len; }
+      else if (b.has_cabac) { const auto& v = decoded[f][blk_slice[i]]; if (!v.empty()) memcpy(o, v.data(), v.size()); o += v.size(); }
+    }
+  });
+  if (nomem) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return AVR_E_NOMEM; }
+  avr_trace("d: assemble");
+  tt.host_ms = now_ms() - t_call0 - (tt.h2d_ms + tt.kernel_ms + tt.d2h_ms);
   if (tacc) *tacc = tt;
   return AVR_OK;
 }

@@ -32,18 +32,19 @@ struct AvrParseResult {
 
 struct AvrParShared {
   uint8_t st[1024];
-  uint8_t range_lps[256];
+  uint8_t range_lps[256];              // [pStateIdx][qRangeIdx]; read as one 32-bit row per state
   uint8_t trans_lps[64];
-  // standard CABAC decoding engine (ITU-T H.264 9.3.3.2)
-  uint32_t range, offset;
-  uint64_t bitbuf; int nbits;          // unread bits, right-aligned
+  // CABAC decoding engine (ITU-T H.264 9.3.3.2) in left-aligned form: val bits 31..23 = codIOffset, the bits
+  // below are read-ahead; "offset >= range" is val >= range << 23 and renormalisation is a plain shift
+  uint32_t val, range, nextw;          // nextw = the 16 bits that follow the valid ones (loaded one refill ahead)
+  int nvalid;                          // valid bits in val, from the top (>= 17 between bins)
   const uint8_t* in; uint32_t pos, size; uint32_t tail;
   // recorder (avr_record.h Recorder)
   uint16_t* bins; uint32_t nb, bin_cap, file_bin_base;
   AvrBlock* blocks; uint32_t nblk, blk_cap;
   uint32_t emitted, frame, mb_addr; int mb_w;
   int cat, n, max_coeff, is_dc;
-  int in_sigmap, expect_eob, overflow;
+  int in_sigmap, expect_eob;
 };
 
 #if defined(__CUDACC__)
@@ -58,103 +59,190 @@ static AvrParShared g_par;
 #define AVR_PAR_M inline
 #endif
 
-AVR_PAR_INL uint32_t avr_par_byte(uint32_t pos) {
-  if (pos < g_par.size) return g_par.in[pos];
-  const uint32_t k = pos - g_par.size;
-  return k < 4 ? (g_par.tail >> (8 * k)) & 0xFF : 0u;
+// Engine registers: live in g_par between the parser's single-bin calls, in registers across a residual block.
+struct AvrParRegs { uint32_t val, range, nextw, pos, nb; int nvalid; };
+AVR_PAR_INL void avr_par_load(AvrParRegs& r) {
+  r.val = g_par.val; r.range = g_par.range; r.nextw = g_par.nextw; r.pos = g_par.pos; r.nb = g_par.nb; r.nvalid = g_par.nvalid;
 }
-AVR_PAR_INL uint32_t avr_par_bits(int n) {
-  if (n == 0) return 0;
-  while (g_par.nbits < n) {
-    g_par.bitbuf = (g_par.bitbuf << 8) | avr_par_byte(g_par.pos++);
-    g_par.nbits += 8;
+AVR_PAR_INL void avr_par_store(const AvrParRegs& r) {
+  g_par.val = r.val; g_par.range = r.range; g_par.nextw = r.nextw; g_par.pos = r.pos; g_par.nb = r.nb; g_par.nvalid = r.nvalid;
+}
+// two stream bytes at pos, big-endian; past `size` come the bytes libavcodec's buffer holds there, then zeros
+AVR_PAR_INL uint32_t avr_par_word(uint32_t pos) {
+  if (pos + 1 < g_par.size) return ((uint32_t)g_par.in[pos] << 8) | g_par.in[pos + 1];
+  uint32_t w = 0;
+  for (uint32_t k = 0; k < 2; k++) {
+    const uint32_t q = pos + k;
+    const uint32_t b = q < g_par.size ? g_par.in[q] : q - g_par.size < 4 ? (g_par.tail >> (8 * (q - g_par.size))) & 0xFF : 0u;
+    w = (w << 8) | b;
   }
-  g_par.nbits -= n;
-  return (uint32_t)(g_par.bitbuf >> g_par.nbits) & ((1u << n) - 1);
+  return w;
 }
-AVR_PAR_INL void avr_par_emit(int ctx, int sym) {
-  int kind = AVR_KIND_DEFAULT;
-  if (g_par.in_sigmap) {
-    kind = g_par.expect_eob ? AVR_KIND_SIG_EOB : AVR_KIND_SIG_MAP;
-    g_par.expect_eob = !g_par.expect_eob && sym;
-    if (g_par.nblk <= g_par.blk_cap && g_par.nblk > 0) g_par.blocks[g_par.nblk - 1].nbins++;
+AVR_PAR_INL void avr_par_refill(AvrParRegs& r) {
+  if (r.nvalid <= 16) {
+    r.val |= r.nextw << (16 - r.nvalid);
+    r.nvalid += 16;
+    r.pos += 2;
+    r.nextw = avr_par_word(r.pos);      // used one refill later: its latency stays off the bin chain
   }
-  if (g_par.nb < g_par.bin_cap) g_par.bins[g_par.nb] = AVR_BIN(sym, ctx, kind); else g_par.overflow = 1;
-  g_par.nb++;
-  if (kind != AVR_KIND_SIG_EOB) g_par.emitted++;
 }
-AVR_PAR_FN int avr_par_get(int ctx) {
-  uint32_t s = g_par.st[ctx], p = s >> 1, mps = s & 1;
-  uint32_t range = g_par.range, offset = g_par.offset;
-  const uint32_t lps = g_par.range_lps[(p << 2) | ((range >> 6) & 3)];
-  range -= lps;
-  int bin;
-  if (offset >= range) {
-    bin = (int)(mps ^ 1); offset -= range; range = lps;
-    if (p == 0) mps ^= 1;
-    p = g_par.trans_lps[p];
+AVR_PAR_INL void avr_par_engine_init(AvrParRegs& r) {
+  r.val = (avr_par_word(0) << 16) | avr_par_word(2);
+  r.nvalid = 32; r.pos = 4; r.nextw = avr_par_word(4);
+  r.range = 510; r.nb = 0;
+}
+AVR_PAR_INL void avr_par_put(AvrParRegs& r, uint32_t rec) {
+  const uint32_t i = r.nb < g_par.bin_cap ? r.nb : g_par.bin_cap - 1;   // past the capacity: keep counting, status says overflow
+  g_par.bins[i] = (uint16_t)rec;
+  r.nb++;
+}
+// DecodeDecision (9.3.3.2.1) on the state byte (pStateIdx << 1 | valMPS)
+AVR_PAR_INL int avr_par_decision(AvrParRegs& r, int ctx) {
+  const uint32_t s = g_par.st[ctx];
+  const uint32_t row = reinterpret_cast<const uint32_t*>(g_par.range_lps)[s >> 1];
+  const uint32_t lps = (row >> ((r.range >> 3) & 24)) & 0xFF;
+  uint32_t range = r.range - lps;
+  const uint32_t scaled = range << 23;
+  uint32_t bin = s & 1, ns;
+  if (r.val >= scaled) {
+    r.val -= scaled; range = lps; bin ^= 1;
+    ns = ((uint32_t)g_par.trans_lps[s >> 1] << 1) | ((s & 1) ^ (uint32_t)((s >> 1) == 0));
   } else {
-    bin = (int)mps;
-    if (p < 62) p++;
+    ns = s < 124 ? s + 2 : s;
   }
-  g_par.st[ctx] = (uint8_t)((p << 1) | mps);
-  if (range < 256) {
-    const int sh = AVR_CLZ32(range) - 23;
-    range <<= sh;
-    offset = (offset << sh) | avr_par_bits(sh);
-  }
-  g_par.range = range; g_par.offset = offset;
-  avr_par_emit(ctx, bin);
+  g_par.st[ctx] = (uint8_t)ns;
+  const int sh = AVR_CLZ32(range) - 23;          // 0 when range >= 256
+  r.range = range << sh; r.val <<= sh; r.nvalid -= sh;
+  avr_par_refill(r);
+  return (int)bin;
+}
+AVR_PAR_INL int avr_par_bypass_r(AvrParRegs& r) {
+  const uint32_t scaled = r.range << 22;         // (offset << 1 | bit) >= range  <=>  val >= range << 22
+  int bin = 0;
+  if (r.val >= scaled) { r.val -= scaled; bin = 1; }
+  r.val <<= 1; r.nvalid -= 1;
+  avr_par_refill(r);
+  return bin;
+}
+AVR_PAR_INL int avr_par_terminate_r(AvrParRegs& r) {
+  const uint32_t range = r.range - 2;
+  if (r.val >= (range << 23)) { r.range = range; return 1; }
+  const int sh = range < 256 ? 1 : 0;
+  r.range = range << sh; r.val <<= sh; r.nvalid -= sh;
+  avr_par_refill(r);
+  return 0;
+}
+
+// ---- single-bin entry points for the syntax walk outside residual blocks ---------------------
+AVR_PAR_FN int avr_par_get(int ctx) {
+  AvrParRegs r; avr_par_load(r);
+  const int bin = avr_par_decision(r, ctx);
+  avr_par_put(r, AVR_BIN(bin, ctx, AVR_KIND_DEFAULT));
+  avr_par_store(r);
+  g_par.emitted++;
   return bin;
 }
 AVR_PAR_FN int avr_par_bypass() {
-  uint32_t offset = (g_par.offset << 1) | avr_par_bits(1);
-  int bin = 0;
-  if (offset >= g_par.range) { offset -= g_par.range; bin = 1; }
-  g_par.offset = offset;
-  avr_par_emit(AVR_CTX_BYPASS, bin);
+  AvrParRegs r; avr_par_load(r);
+  const int bin = avr_par_bypass_r(r);
+  avr_par_put(r, AVR_BIN(bin, AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+  avr_par_store(r);
+  g_par.emitted++;
   return bin;
 }
 AVR_PAR_FN int avr_par_terminate() {
-  uint32_t range = g_par.range - 2;
-  int bin;
-  if (g_par.offset >= range) bin = 1;
-  else {
-    bin = 0;
-    if (range < 256) { range <<= 1; g_par.offset = (g_par.offset << 1) | avr_par_bits(1); }
-  }
-  g_par.range = range;
-  avr_par_emit(AVR_CTX_TERMINATE, bin);
+  AvrParRegs r; avr_par_load(r);
+  const int bin = avr_par_terminate_r(r);
+  avr_par_put(r, AVR_BIN(bin, AVR_CTX_TERMINATE, AVR_KIND_DEFAULT));
+  avr_par_store(r);
+  g_par.emitted++;
   return bin;
 }
-AVR_PAR_FN void avr_par_sigmap_begin() {
+
+// ---- one residual block (h264_cabac.c:1583-1780; recorder: Recorder::begin_sub_mb / sigmap in avr_record.h) ----
+// Engine registers stay in registers for the whole block; the block record is written once.
+AVR_PAR_FN int avr_par_residual_block(int cat, int n, int max_coeff, int is_dc, int sig_base, int last_base, int abs_base) {
+  AvrParRegs r; avr_par_load(r);
+  const uint32_t bin_start = g_par.file_bin_base + r.nb;
+  const int coefs = max_coeff - 1;
+  int coeff_count = 0, last;
+  for (last = 0; last < coefs; last++) {
+    int sig_ctx = sig_base + last, last_ctx = last_base + last;
+    if (max_coeff == 64) {
+      sig_ctx = sig_base + avr_sig8x8_off(last);
+      last_ctx = last_base + (last == 0 ? 0 : last < 16 ? 1 : last < 32 ? 2 : last < 40 ? 3 : last < 48 ? 4 : last < 52 ? 5 : last < 56 ? 6 : last < 60 ? 7 : 8);
+    }
+    const int sig = avr_par_decision(r, sig_ctx);
+    avr_par_put(r, AVR_BIN(sig, sig_ctx, AVR_KIND_SIG_MAP));
+    if (sig) {
+      coeff_count++;
+      const int eob = avr_par_decision(r, last_ctx);
+      avr_par_put(r, AVR_BIN(eob, last_ctx, AVR_KIND_SIG_EOB));
+      if (eob) { last = max_coeff; break; }
+    }
+  }
+  const uint32_t map_bins = g_par.file_bin_base + r.nb - bin_start;
+  uint32_t emitted = (uint32_t)avr_nz_bits(max_coeff) + map_bins - (uint32_t)coeff_count;   // EOB bins are inferred, not coded
+  if (last == max_coeff - 1) coeff_count++;
   if (g_par.nblk < g_par.blk_cap) {
     AvrBlock b;
-    b.bin_start = g_par.file_bin_base + g_par.nb;
-    b.mb_addr = g_par.mb_addr;
-    b.frame = g_par.frame;
-    b.n = (uint8_t)g_par.n;
-    b.cat_flags = (uint8_t)(g_par.cat | (g_par.is_dc << 4));
-    b.max_coeff = (uint8_t)g_par.max_coeff;
-    b.nbins = 0;
+    b.bin_start = bin_start; b.mb_addr = g_par.mb_addr; b.frame = g_par.frame;
+    b.n = (uint8_t)n; b.cat_flags = (uint8_t)(cat | (is_dc << 4)); b.max_coeff = (uint8_t)max_coeff;
+    b.nbins = (uint8_t)map_bins;
     g_par.blocks[g_par.nblk] = b;
-  } else g_par.overflow = 1;
+  }
   g_par.nblk++;
-  g_par.in_sigmap = 1; g_par.expect_eob = 0;
-  g_par.emitted += (uint32_t)avr_nz_bits(g_par.max_coeff);
+  // coeff_abs_level_minus1 + sign, reverse scan order (h264_cabac.c:1727-1768)
+  const uint32_t lvl_start = r.nb;
+  int node_ctx = 0;
+  const int gt1_max = cat == 3 ? 8 : 9;
+  for (int c = coeff_count; c > 0; c--) {
+    const int ctx1 = abs_base + (node_ctx < 4 ? node_ctx + 1 : 0);
+    const int b0 = avr_par_decision(r, ctx1);
+    avr_par_put(r, AVR_BIN(b0, ctx1, AVR_KIND_DEFAULT));
+    if (b0 == 0) {
+      node_ctx = node_ctx < 3 ? node_ctx + 1 : node_ctx;
+    } else {
+      const int gt1 = node_ctx < 4 ? 5 : (node_ctx + 2 > gt1_max ? gt1_max : node_ctx + 2);
+      const int ctx2 = abs_base + gt1;
+      node_ctx = node_ctx < 4 ? 4 : (node_ctx < 7 ? node_ctx + 1 : 7);
+      int coeff_abs = 2;
+      while (coeff_abs < 15) {
+        const int b = avr_par_decision(r, ctx2);
+        avr_par_put(r, AVR_BIN(b, ctx2, AVR_KIND_DEFAULT));
+        if (!b) break;
+        coeff_abs++;
+      }
+      if (coeff_abs >= 15) {
+        int j = 0;
+        for (;;) {
+          const int b = avr_par_bypass_r(r);
+          avr_par_put(r, AVR_BIN(b, AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+          if (!b || j >= 30) break;
+          j++;
+        }
+        while (j--) avr_par_put(r, AVR_BIN(avr_par_bypass_r(r), AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+      }
+    }
+    avr_par_put(r, AVR_BIN(avr_par_bypass_r(r), AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+  }
+  emitted += r.nb - lvl_start;
+  g_par.emitted += emitted;
+  avr_par_store(r);
+  return coeff_count;
 }
 
 struct AvrParsePolicy {
-  static constexpr bool kFastResidual = false;
-  AVR_PAR_M int residual_block(int, int, int, int, int, int, int) { return 0; }
+  static constexpr bool kFastResidual = true;
+  AVR_PAR_M int residual_block(int cat, int n, int mc, int dc, int sig, int last, int abs_) { return avr_par_residual_block(cat, n, mc, dc, sig, last, abs_); }
   AVR_PAR_M int get(int ctx) { return avr_par_get(ctx); }
   AVR_PAR_M int bypass(int) { return avr_par_bypass(); }
   AVR_PAR_M int terminate(int) { return avr_par_terminate(); }
   AVR_PAR_M void mb_begin(int x, int y) { g_par.mb_addr = (uint32_t)(x + y * g_par.mb_w); }
-  AVR_PAR_M void sub_mb_begin(int cat, int n, int mc, int dc, int) { g_par.cat = cat; g_par.n = n; g_par.max_coeff = mc; g_par.is_dc = dc; }
+  AVR_PAR_M void sub_mb_begin(int, int, int, int, int) {}
   AVR_PAR_M void sub_mb_end() {}
-  AVR_PAR_M void sigmap_begin() { avr_par_sigmap_begin(); }
-  AVR_PAR_M void sigmap_end() { g_par.in_sigmap = 0; }
+  AVR_PAR_M void sigmap_begin() {}
+  AVR_PAR_M void sigmap_end() {}
   AVR_PAR_M void hint(int, int) {}
 };
 
@@ -162,18 +250,17 @@ struct AvrParsePolicy {
 // the kernel).  row = [mb_w] MbInfo scratch private to this slice (neighbours never cross slices).
 AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
                                 avr::MbInfo* row, AvrParseResult* res) {
-  g_par.in = raw + ps.raw_off; g_par.pos = 0; g_par.size = ps.size;
+  g_par.in = raw + ps.raw_off; g_par.size = ps.size;
   g_par.tail = (uint32_t)ps.tail[0] | ((uint32_t)ps.tail[1] << 8) | ((uint32_t)ps.tail[2] << 16) | ((uint32_t)ps.tail[3] << 24);
-  g_par.bitbuf = 0; g_par.nbits = 0;
-  g_par.range = 510; g_par.offset = avr_par_bits(9);
-  g_par.bins = bins_pool + ps.bin_off; g_par.nb = 0; g_par.bin_cap = ps.bin_cap; g_par.file_bin_base = ps.file_bin_base;
+  g_par.bins = bins_pool + ps.bin_off; g_par.bin_cap = ps.bin_cap; g_par.file_bin_base = ps.file_bin_base;
   g_par.blocks = blk_pool + ps.blk_off; g_par.nblk = 0; g_par.blk_cap = ps.blk_cap;
   g_par.emitted = 0; g_par.frame = ps.frame; g_par.mb_addr = 0; g_par.mb_w = ps.sp.mb_w;
-  g_par.in_sigmap = 0; g_par.expect_eob = 0; g_par.overflow = 0;
+  { AvrParRegs r; avr_par_engine_init(r); avr_par_store(r); }
   for (int x = 0; x < ps.sp.mb_w; x++) row[x].uid = 0;
   AvrParsePolicy io;
   avr::SliceParser<AvrParsePolicy> parser(io, ps.sp, row, 1);
   const int rc = parser.run();
   res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted;
-  res->status = g_par.overflow ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;
+  const int over = g_par.nb > g_par.bin_cap || g_par.nblk > g_par.blk_cap;
+  res->status = over ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;
 }

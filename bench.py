@@ -223,9 +223,13 @@ def main():
             barrier()
             t0 = time.perf_counter()
             comp, tcf = A.compress_files(ctx, blobs)
+            t1 = time.perf_counter()
             back, tdf = A.decompress_files(ctx, comp)
             torch.cuda.synchronize()
             e2e_t.append(time.perf_counter() - t0)
+            e2e_parts = {"compress_wall_ms": (t1 - t0) * 1e3, "decompress_wall_ms": (time.perf_counter() - t1) * 1e3,
+                         "compress": {k: round(tcf[k], 3) for k in ("host_ms", "h2d_ms", "parse_ms", "kernel_ms", "d2h_ms")},
+                         "decompress": {k: round(tdf[k], 3) for k in ("host_ms", "h2d_ms", "kernel_ms", "d2h_ms")}}
             h2d = tcf["h2d_bytes"] + tdf["h2d_bytes"]; d2h = tcf["d2h_bytes"] + tdf["d2h_bytes"]
         assert back == blobs, "e2e roundtrip is not bit-exact"
         e2e_s = min(e2e_t)
@@ -279,7 +283,7 @@ def main():
         "compress_gbins_s": bins / (c_ms / 1e3 / args.steps) / 1e9, "decompress_gbins_s": bins / (d_ms / 1e3 / args.steps) / 1e9,
         "bit_exact": True,
         "e2e": {"value": total_mb_all / e2e_s, "unit": "MB/s", "h2d_bytes_per_step": int(h2d_all), "d2h_bytes_per_step": int(d2h_all),
-                "gbins_s": bins_all / e2e_s / 1e9, "host_threads": cores},
+                "gbins_s": bins_all / e2e_s / 1e9, "host_threads": cores, "rank0_parts": e2e_parts},
         "gpu_launches": int(launches_all),
         "clocks": clocks,
         "roofline": {"kernel": "avr_k_decompress_chain", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
