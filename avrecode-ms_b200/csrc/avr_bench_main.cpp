@@ -1,6 +1,6 @@
 // avrbench: native timing / profiling harness over the C ABI (no Python in the process, so it can
 // run under ncu and compute-sanitizer).
-//   avrbench <reps> <mode: 0 pipeline | 1 chain | 2 decompress only> <clip.h264>...
+//   avrbench <reps> <mode: 0 pipeline | 1 chain | 2 decompress only | 3 file API (device parse)> <clip.h264>...
 // Stages the clips' records once, runs compress `reps` times, stages the payloads, runs
 // decompress `reps` times, verifies the re-encoded CABAC bytes against the input files and
 // prints one line of JSON with the CUDA-event times.
@@ -38,6 +38,27 @@ int main(int argc, char** argv) {
   }
   avr_context* ctx;
   CHECK(avr_context_create(0, &ctx));
+  if (mode == 3) {
+    // the public file-level calls: raw files in, containers out, and back; every kernel of the product path launches
+    std::vector<const uint8_t*> in((size_t)n), cin((size_t)n); std::vector<size_t> len((size_t)n), clen((size_t)n);
+    for (int i = 0; i < n; i++) { in[i] = data[i].data(); len[i] = data[i].size(); }
+    std::vector<avr_buffer> comp((size_t)n), back((size_t)n);
+    avr_timing tc, td; int bad = 0;
+    for (int r = 0; r < reps; r++) {
+      CHECK(avr_compress_files(ctx, in.data(), len.data(), n, 8, comp.data(), &tc));
+      for (int i = 0; i < n; i++) { cin[i] = comp[i].data; clen[i] = comp[i].size; }
+      CHECK(avr_decompress_files(ctx, cin.data(), clen.data(), n, 8, back.data(), &td));
+      for (int i = 0; i < n; i++) {
+        bad += back[i].size != len[i] || memcmp(back[i].data, in[i], len[i]) != 0;
+        avr_buffer_free(&comp[i]); avr_buffer_free(&back[i]);
+      }
+    }
+    printf("{\"files\": %d, \"bins\": %llu, \"bytes\": %llu, \"parse_ms\": %.3f, \"compress_kernel_ms\": %.3f, \"coder_ms\": %.3f, "
+           "\"decompress_kernel_ms\": %.3f, \"launches\": %u, \"bad_files\": %d}\n", n, (unsigned long long)tc.bins,
+           (unsigned long long)bytes, tc.parse_ms, tc.kernel_ms, tc.coder_launch_ms_x1000 / 1000.0, td.kernel_ms, tc.launches + td.launches, bad);
+    avr_context_destroy(ctx);
+    return bad ? 1 : 0;
+  }
   avr_cbatch* cb;
   CHECK(avr_cbatch_create(ctx, recs.data(), n, &cb));
   avr_timing tc; memset(&tc, 0, sizeof tc);
