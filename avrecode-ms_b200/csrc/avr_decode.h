@@ -18,10 +18,12 @@
 // Include only from avr_kernels.cu (device: state in __shared__, one chain per block) and from
 // tests/host_emul.cpp (host: same code on a static object, the encoder runs inline).
 #pragma once
+#include <stddef.h>
 #include "avr_bodies.h"
 
 #define AVR_RING_LOG 10
 #define AVR_RING (1u << AVR_RING_LOG)
+#define AVR_RING_EMPTY 0xFFFFFFFFu
 #define AVR_REC_ABORT 2047u          // ctx code: chain failed, encoder must stop
 
 struct AvrCabRegs {                  // CABAC encoder state (registers of the encoder thread)
@@ -30,11 +32,13 @@ struct AvrCabRegs {                  // CABAC encoder state (registers of the en
   int err;
 };
 
+struct alignas(16) AvrMs { uint64_t m, s; };               // divisor constants of one total, one 16-byte load (avr_div_tab.h)
 struct AvrDecShared {
   AvrHotTabs hot;                              // per-bin constant tables
+  AvrMs ms[98];                                // hot.div again, one entry per total
   uint16_t est_def[AVR_NUM_CTX_KEYS + 2];      // estimators of the 1026 default keys (file lifetime)
   uint8_t st[1024];                            // CABAC context states of the current slice (encoder thread)
-  uint32_t ring[AVR_RING];                     // (lap tag << 16) | (ctx << 1) | symbol
+  uint32_t ring[AVR_RING];                     // (ctx << 1) | symbol, or AVR_RING_EMPTY; the consumer empties what it has read
   uint32_t ring_head, ring_tail_seen;          // producer side
   volatile uint32_t ring_tail;                 // consumer progress (back-pressure)
   // range decoder (arithmetic_code.h:220-288)
@@ -50,6 +54,7 @@ struct AvrDecShared {
   uint32_t mb_addr;
   uint32_t bins;
   int done;
+  uint64_t self;                               // shared-window address of this object, read back as an opaque value (see avr_sbase)
 };
 
 #if defined(__CUDACC__)
@@ -137,8 +142,7 @@ AVR_DEC_INL void avr_ring_post(uint32_t ctx, int symbol) {
     do { t = g_dec.ring_tail; } while (head - t >= AVR_RING - 1);
     g_dec.ring_tail_seen = t;
   }
-  const uint32_t tag = ((head >> AVR_RING_LOG) + 1) & 0xFFFF;
-  reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (tag << 16) | (ctx << 1) | (uint32_t)symbol;
+  reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (ctx << 1) | (uint32_t)symbol;
   g_dec.ring_head = head + 1;
 #else
   avr_cab_consume(g_cab_host, (ctx << 1) | (uint32_t)symbol);
@@ -153,11 +157,10 @@ AVR_DEC_INL void avr_ring_post_r(uint32_t& head, uint32_t& tail_seen, uint32_t c
     do { t = g_dec.ring_tail; } while (head - t >= AVR_RING - 1);
     tail_seen = t;
   }
-  const uint32_t tag = ((head >> AVR_RING_LOG) + 1) & 0xFFFF;
-  reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (tag << 16) | (ctx << 1) | (uint32_t)symbol;
+  reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (ctx << 1) | (uint32_t)symbol;
   head++;
 #else
-  (void)head; (void)tail_seen;
+  (void)tail_seen; head++;
   avr_cab_consume(g_cab_host, (ctx << 1) | (uint32_t)symbol);
 #endif
 }
@@ -170,9 +173,10 @@ static __device__ __noinline__ void avr_cab_encoder_thread(uint8_t* out, uint32_
   uint32_t tail = g_dec.ring_tail;
   volatile uint32_t* ring = reinterpret_cast<volatile uint32_t*>(g_dec.ring);
   for (;;) {
-    const uint32_t tag = ((tail >> AVR_RING_LOG) + 1) & 0xFFFF;
-    uint32_t rec = ring[tail & (AVR_RING - 1)];
-    while ((rec >> 16) != tag) { __nanosleep(64); rec = ring[tail & (AVR_RING - 1)]; }
+    const uint32_t slot = tail & (AVR_RING - 1);
+    uint32_t rec = ring[slot];
+    while (rec == AVR_RING_EMPTY) { __nanosleep(32); rec = ring[slot]; }
+    ring[slot] = AVR_RING_EMPTY;       // before the tail moves: the producer reuses a slot only after it has seen the tail pass it
     tail++;
     if ((tail & 63) == 0) g_dec.ring_tail = tail;
     if (avr_cab_consume(c, rec)) break;
@@ -245,8 +249,8 @@ AVR_DEC_INL int avr_dec_default(uint64_t& low, uint64_t& range, uint32_t key) { 
   g_dec.est_def[key] = (uint16_t)avr_cell_update(cell, symbol, 0x60);
   return symbol;
 }
-AVR_DEC_INL int avr_dec_global(uint64_t& low, uint64_t& range, uint32_t key, uint32_t limit) {
-  uint16_t* c = g_dec.est + key;
+AVR_DEC_INL int avr_dec_global(uint64_t& low, uint64_t& range, uint16_t* est, uint32_t key, uint32_t limit) {
+  uint16_t* c = est + key;
   const uint32_t cell = *c;
   const int symbol = avr_dec_symbol(low, range, cell);
   *c = (uint16_t)avr_cell_update(cell, symbol, limit);
@@ -280,40 +284,173 @@ AVR_DEC_FN int avr_dec_terminate() {
   return sym;
 }
 
+// ---- address-space explicit accessors for the residual-block loops -------------------------------
+// On the device: ld/st.shared with a 32-bit shared-window address and ld/st.global.  With plain C++
+// accesses ptxas re-derived the shared window base from SR_CgaCtaId inside the loops (an S2R per bin)
+// and used generic LD/ST with a per-iteration descriptor set-up for the estimator pool
+// (tools/sass_model.py on the v6 build).  On the host: plain memory.
+#if defined(__CUDA_ARCH__)
+typedef uint32_t avr_sptr;
+AVR_DEC_INL avr_sptr avr_sp(const void* p) { return (avr_sptr)__cvta_generic_to_shared(p); }
+AVR_DEC_INL uint32_t avr_s_ld16(avr_sptr a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory"); return v; }
+AVR_DEC_INL void avr_s_st16(avr_sptr a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v) : "memory"); }
+AVR_DEC_INL void avr_s_st32(avr_sptr a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+AVR_DEC_INL void avr_s_ld_ms(avr_sptr a, uint64_t& m, uint32_t& sh) {     // read-only table: free to schedule
+  uint64_t t; asm("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(m), "=l"(t) : "r"(a)); sh = (uint32_t)t;
+}
+AVR_DEC_INL uint32_t avr_g_ld16(const uint16_t* p) { uint16_t v; asm volatile("ld.global.u16 %0, [%1];" : "=h"(v) : "l"(p) : "memory"); return v; }
+AVR_DEC_INL void avr_g_st16(uint16_t* p, uint32_t v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(p), "h"((uint16_t)v) : "memory"); }
+#else
+typedef uintptr_t avr_sptr;
+AVR_DEC_INL avr_sptr avr_sp(const void* p) { return (avr_sptr)p; }
+AVR_DEC_INL uint32_t avr_s_ld16(avr_sptr a) { return *reinterpret_cast<const uint16_t*>(a); }
+AVR_DEC_INL void avr_s_st16(avr_sptr a, uint32_t v) { *reinterpret_cast<uint16_t*>(a) = (uint16_t)v; }
+AVR_DEC_INL void avr_s_st32(avr_sptr a, uint32_t v) { *reinterpret_cast<uint32_t*>(a) = v; }
+AVR_DEC_INL void avr_s_ld_ms(avr_sptr a, uint64_t& m, uint32_t& sh) { const AvrMs* e = reinterpret_cast<const AvrMs*>(a); m = e->m; sh = (uint32_t)e->s; }
+AVR_DEC_INL uint32_t avr_g_ld16(const uint16_t* p) { return *p; }
+AVR_DEC_INL void avr_g_st16(uint16_t* p, uint32_t v) { *p = (uint16_t)v; }
+#endif
+AVR_DEC_INL void avr_ms_fill() {     // chain thread, once per file
+  for (uint32_t t = 0; t < 98; t++) { g_dec.ms[t].m = g_dec.hot.div.m[t]; g_dec.ms[t].s = g_dec.hot.div.s[t]; }
+}
+
 // ---- one residual block (ffmpeg h264_cabac.c:1583-1780 walk; reference order recode.cpp:1483-1499)
 // nnz side channel -> significance map (EOB bins inferred: recode.cpp:1444-1445) -> levels/signs.
-// low/range stay in registers for the whole block.  Returns coeff_count.
+// Returns coeff_count.
+//
+// One chain thread issues in order, so what bounds a bin is the length of the DEPENDENT instruction
+// sequence plus the fixed cost of every branch (predicate latency ~13 cycles + BRA 5 + BSSY/BSYNC),
+// not the instruction count.  The only true recurrence is low/range -> symbol -> low/range; the rest is
+// arranged so that it does not wait on it:
+//   * cells and divisor constants (m, s) of BOTH possible next keys are requested before the current
+//     bin is decoded, and selects pick after;
+//   * the bypass estimator and the coeff_abs_level (ctx2) estimator stay in registers across their
+//     runs, with the divisor constants of total+1 requested before the symbol is known;
+//   * one branch per significance-map position covers everything unusual (renormalisation, end of
+//     block, 8x8 offset repeat); ring space is reserved per block / per coefficient, not per bin; the
+//     EOB record is stored unconditionally (AVR_RING_EMPTY when there is none).
+struct AvrEstReg { uint32_t cell; uint64_t m; uint32_t s; };
+AVR_DEC_INL void avr_est_consts(avr_sptr s_ms, AvrEstReg& e) {
+  const uint32_t tot = (e.cell & 0xFF) + (e.cell >> 8);
+  avr_s_ld_ms(s_ms + tot * 16u, e.m, e.s);
+}
+AVR_DEC_INL int avr_dec_core(uint64_t& low, uint64_t& range, const AvrEstReg& e) {   // arithmetic_code.h:232-248 without the renormalisation
+  const uint64_t r1 = (AVR_MULHI64(range, e.m) >> e.s) * (uint64_t)(e.cell & 0xFF);
+  const uint64_t r0 = range - r1;
+  const int symbol = low >= r0;
+  low -= symbol ? r0 : 0ull;
+  range = symbol ? r1 : r0;
+  return symbol;
+}
+#define AVR_DEC_RENORM(low_, range_) do { if ((range_) < (1ull << 51)) { const AvrLowRange r_ = avr_dec_refill((low_), (range_), 1ull << 55); (low_) = r_.low; (range_) = r_.range; } } while (0)
+// register-resident estimator: decode one symbol, update, and have the constants of the new total ready
+AVR_DEC_INL int avr_dec_reg(uint64_t& low, uint64_t& range, avr_sptr s_ms, AvrEstReg& e, uint32_t limit) {
+  const uint32_t tot1 = (e.cell & 0xFF) + (e.cell >> 8) + 1;
+  uint64_t m1; uint32_t s1; avr_s_ld_ms(s_ms + tot1 * 16u, m1, s1);          // independent of the symbol
+  const int symbol = avr_dec_core(low, range, e);
+  e.cell += symbol ? 1u : 0x100u; e.m = m1; e.s = s1;
+  if (tot1 > limit) { e.cell = ((e.cell + 0x0101u) >> 1) & 0x7F7Fu; avr_est_consts(s_ms, e); }   // halving: once per ~50 uses of a key
+  return symbol;
+}
+AVR_DEC_INL void avr_ring_reserve(uint32_t head, uint32_t& tail_seen, uint32_t n) {
+#if defined(__CUDACC__)
+  if (head + n - 1 - tail_seen >= AVR_RING - 1) {
+    uint32_t t;
+    do { t = g_dec.ring_tail; } while (head + n - 1 - t >= AVR_RING - 1);
+    tail_seen = t;
+  }
+#else
+  (void)head; (void)tail_seen; (void)n;
+#endif
+}
+// space reserved by the caller; rec = (ctx << 1) | symbol, or AVR_RING_EMPTY (a no-op on a free slot)
+AVR_DEC_INL void avr_ring_store(avr_sptr s_ring, uint32_t slot, uint32_t rec) {
+#if defined(__CUDACC__)
+  avr_s_st32(s_ring + ((slot & (AVR_RING - 1)) << 2), rec);
+#else
+  (void)s_ring; (void)slot;
+  if (rec != AVR_RING_EMPTY) avr_cab_consume(g_cab_host, rec);
+#endif
+}
+
+// both outcomes of the estimator update, computed while the symbol is still unknown (recode.cpp:1037-1054)
+AVR_DEC_INL void avr_cell_update2(uint32_t cell, uint32_t limit, uint32_t& u0, uint32_t& u1) {
+  const bool halve = (cell & 0xFF) + (cell >> 8) + 1 > limit;
+  u0 = cell + 0x100u; u1 = cell + 1u;
+  if (halve) { u0 = ((u0 + 0x0101u) >> 1) & 0x7F7Fu; u1 = ((u1 + 0x0101u) >> 1) & 0x7F7Fu; }
+}
+// The shared-window address of g_dec, loaded from g_dec itself: an address ptxas cannot rematerialise from
+// SR_CgaCtaId inside the loops (it did, one S2UR + ULEA per bin, when the address came from cvta).
+AVR_DEC_INL avr_sptr avr_sbase() { return (avr_sptr)g_dec.self; }
+#define AVR_S_OFF(member) ((avr_sptr)offsetof(AvrDecShared, member))
+
+template <bool IS64>
+AVR_DEC_INL int avr_dec_sigmap(uint64_t& low, uint64_t& range, uint32_t& head, uint16_t* est, avr_sptr s_ms, avr_sptr s_ring,
+                               uint32_t key0, int stored, int max_coeff, int sig_base, int last_base, int* last_out) {
+  const int coefs = max_coeff - 1;
+  int count = 0, last = 0;
+  int zz = IS64 ? avr_sig8x8_off(0) : 0;
+  uint32_t rowk = key0;                                          // key of (count, offset 0)
+  uint32_t k = rowk + (uint32_t)zz;                              // the current position's key
+  AvrEstReg e; e.cell = avr_g_ld16(est + k); avr_est_consts(s_ms, e);
+  for (;;) {
+    // both candidates for the next position, requested before this bin is decoded (always inside the pool)
+    const int nlast = last + 1;
+    const int nzz = IS64 ? avr_sig8x8_off(nlast) : nlast;
+    const uint32_t ka = rowk + (uint32_t)nzz, kb = ka + 16u;
+    AvrEstReg ea, eb; ea.cell = avr_g_ld16(est + ka); eb.cell = avr_g_ld16(est + kb);
+    avr_est_consts(s_ms, ea); avr_est_consts(s_ms, eb);
+    // everything that depends on the symbol only through a select, before the symbol
+    const int last_ctx = last_base + (!IS64 ? last : last == 0 ? 0 : last < 16 ? 1 : last < 32 ? 2 : last < 40 ? 3 : last < 48 ? 4 : last < 52 ? 5 : last < 56 ? 6 : last < 60 ? 7 : 8);
+    uint32_t u0, u1; avr_cell_update2(e.cell, 0x50, u0, u1);
+    const bool last_pos = nlast >= coefs;
+    const bool eob1 = stored == count + 1;                       // the EOB bin that follows a 1 is inferred, never range-coded
+    const uint32_t rec1 = (uint32_t)(sig_base + zz) << 1;
+    const uint32_t rec2 = ((uint32_t)last_ctx << 1) | (uint32_t)eob1;
+    const bool stop1 = eob1 | last_pos;
+    const bool stop0 = last_pos | (IS64 && nzz == zz);           // 8x8 offsets repeat: the next key would be the cell just written
+    // this bin
+    const int sig = avr_dec_core(low, range, e);
+    avr_g_st16(est + k, sig ? u1 : u0);
+    avr_ring_store(s_ring, head, rec1 | (uint32_t)sig);
+    avr_ring_store(s_ring, head + 1, sig ? rec2 : AVR_RING_EMPTY);
+    head += 1u + (uint32_t)sig;
+    count += sig;
+    last = nlast;
+    if ((sig ? stop1 : stop0) | (range < (1ull << 51))) {        // one branch for everything unusual
+      AVR_DEC_RENORM(low, range);
+      if (sig && eob1) { last = max_coeff; break; }
+      if (last_pos) break;
+      if (IS64 && !sig && nzz == zz) { e.cell = u0; avr_est_consts(s_ms, e); continue; }
+    }
+    e = sig ? eb : ea; k = sig ? kb : ka; rowk += sig ? 16u : 0u; zz = nzz;
+  }
+  *last_out = last;
+  return count;
+}
+
 AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, int sig_base, int last_base, int abs_base) {
   uint64_t low = g_dec.low, range = g_dec.range;
-  uint32_t bins = 0, head = g_dec.ring_head, tail_seen = g_dec.ring_tail_seen;
+  uint32_t head = g_dec.ring_head, tail_seen = g_dec.ring_tail_seen;
+  const uint32_t head0 = head;                                   // every bin of the block is posted once: bins = head - head0
+  uint16_t* const est = g_dec.est;
+  const avr_sptr s_base = avr_sbase();
+  const avr_sptr s_ms = s_base + AVR_S_OFF(ms), s_ring = s_base + AVR_S_OFF(ring), s_def = s_base + AVR_S_OFF(est_def);
   // nnz bits first.  The count is recovered completely (a block that codes as 0 in 2/4 bits is a
   // full one) so that the store holds what the COMPRESSOR held.
   AvrNzCtx nc;
   avr_nz_ctx(&nc, g_dec.store[g_dec.cur], g_dec.store[g_dec.cur ^ 1], g_dec.mb_addr, g_dec.mb_w, n, max_coeff, cat, is_dc, 0);
   const int nbits = avr_nz_bits(max_coeff);
   int stored = 0;
-  for (int k = 0; k < nbits; k++) stored |= avr_dec_global(low, range, avr_nz_bit_key(nc, k, stored), 0x60) << k;
+  for (int k = 0; k < nbits; k++) stored |= avr_dec_global(low, range, est, avr_nz_bit_key(nc, k, stored), 0x60) << k;
   if (stored == 0 && max_coeff <= 16) stored = max_coeff;
   // significance map
   const uint32_t key0 = avr_key_sig(cat, stored, 0, 0);
-  const int coefs = max_coeff - 1;
-  int coeff_count = 0, last;
-  for (last = 0; last < coefs; last++) {
-    int zz_off = last, sig_ctx = sig_base + last, last_ctx = last_base + last;
-    if (max_coeff == 64) {
-      zz_off = avr_sig8x8_off(last); sig_ctx = sig_base + zz_off;
-      last_ctx = last_base + (last == 0 ? 0 : last < 16 ? 1 : last < 32 ? 2 : last < 40 ? 3 : last < 48 ? 4 : last < 52 ? 5 : last < 56 ? 6 : last < 60 ? 7 : 8);
-    }
-    const int sig = avr_dec_global(low, range, key0 + (uint32_t)coeff_count * 16u + (uint32_t)zz_off, 0x50);
-    avr_ring_post_r(head, tail_seen, (uint32_t)sig_ctx, sig);
-    bins++;
-    if (sig) {
-      coeff_count++;
-      const int eob = (stored == coeff_count);                 // inferred, never range-coded
-      avr_ring_post_r(head, tail_seen, (uint32_t)last_ctx, eob);
-      bins++;
-      if (eob) { last = max_coeff; break; }
-    }
+  int coeff_count = 0, last = 0;
+  if (max_coeff > 1) {
+    avr_ring_reserve(head, tail_seen, 2u * (uint32_t)max_coeff);
+    coeff_count = max_coeff == 64 ? avr_dec_sigmap<true>(low, range, head, est, s_ms, s_ring, key0, stored, max_coeff, sig_base, last_base, &last)
+                                  : avr_dec_sigmap<false>(low, range, head, est, s_ms, s_ring, key0, stored, max_coeff, sig_base, last_base, &last);
   }
   if (last == max_coeff - 1) coeff_count++;
   {
@@ -322,50 +459,63 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
     mb[n] = (uint8_t)(coeff_count & 63);
   }
   // coeff_abs_level_minus1 + sign, reverse scan order (h264_cabac.c:1727-1768)
+  const avr_sptr a_byp = s_def + 2u * AVR_CTX_BYPASS, s_abs = s_def + 2u * (uint32_t)abs_base;
+  AvrEstReg byp; byp.cell = avr_s_ld16(a_byp); avr_est_consts(s_ms, byp);
   int node_ctx = 0;
   const int gt1_max = cat == 3 ? 8 : 9;
+  avr_sptr a1 = s_abs + 2u;                                      // ctx1 of node_ctx 0
+  AvrEstReg e1; e1.cell = avr_s_ld16(a1); avr_est_consts(s_ms, e1);
+  const uint32_t rec_abs = (uint32_t)abs_base << 1;
   for (int c = coeff_count; c > 0; c--) {
-    const int ctx1 = abs_base + (node_ctx < 4 ? node_ctx + 1 : 0);
-    const int b0 = avr_dec_default(low, range, (uint32_t)ctx1);
-    avr_ring_post_r(head, tail_seen, (uint32_t)ctx1, b0);
-    bins++;
-    if (b0 == 0) {
-      node_ctx = node_ctx < 3 ? node_ctx + 1 : node_ctx;
-    } else {
-      const int gt1 = node_ctx < 4 ? 5 : (node_ctx + 2 > gt1_max ? gt1_max : node_ctx + 2);
-      const int ctx2 = abs_base + gt1;
-      node_ctx = node_ctx < 4 ? 4 : (node_ctx < 7 ? node_ctx + 1 : 7);
+    avr_ring_reserve(head, tail_seen, 80);                       // one coefficient posts at most 1 + 13 + 61 + 1 records
+    const int i1 = node_ctx < 4 ? node_ctx + 1 : 0;              // ctx1 - abs_base in 0..4, ctx2 - abs_base in 5..9: never the same cell
+    const int i2 = node_ctx < 4 ? 5 : (node_ctx + 2 > gt1_max ? gt1_max : node_ctx + 2);
+    const avr_sptr a2 = s_abs + 2u * (uint32_t)i2;
+    AvrEstReg e2; e2.cell = avr_s_ld16(a2); avr_est_consts(s_ms, e2);   // used only if b0 = 1; its latency hides behind b0
+    uint32_t u0, u1; avr_cell_update2(e1.cell, 0x60, u0, u1);
+    const int b0 = avr_dec_core(low, range, e1);
+    avr_s_st16(a1, b0 ? u1 : u0);
+    avr_ring_store(s_ring, head++, (rec_abs + 2u * (uint32_t)i1) | (uint32_t)b0);
+    // node_ctx and ctx1 of the next coefficient are known now: request that cell behind the store above
+    node_ctx = b0 ? (node_ctx < 4 ? 4 : (node_ctx < 7 ? node_ctx + 1 : 7)) : (node_ctx < 3 ? node_ctx + 1 : node_ctx);
+    a1 = s_abs + 2u * (uint32_t)(node_ctx < 4 ? node_ctx + 1 : 0);
+    e1.cell = avr_s_ld16(a1); avr_est_consts(s_ms, e1);
+    AVR_DEC_RENORM(low, range);
+    if (b0) {
+      const uint32_t rec2 = rec_abs + 2u * (uint32_t)i2;
       int coeff_abs = 2;
       while (coeff_abs < 15) {
-        const int b = avr_dec_default(low, range, (uint32_t)ctx2);
-        avr_ring_post_r(head, tail_seen, (uint32_t)ctx2, b);
-        bins++;
+        const int b = avr_dec_reg(low, range, s_ms, e2, 0x60);
+        avr_ring_store(s_ring, head++, rec2 | (uint32_t)b);
+        AVR_DEC_RENORM(low, range);
         if (!b) break;
         coeff_abs++;
       }
+      avr_s_st16(a2, e2.cell);
       if (coeff_abs >= 15) {
         int j = 0;
         for (;;) {
-          const int b = avr_dec_default(low, range, AVR_CTX_BYPASS);
-          avr_ring_post_r(head, tail_seen, AVR_CTX_BYPASS, b);
-          bins++;
+          const int b = avr_dec_reg(low, range, s_ms, byp, 0x60);
+          avr_ring_store(s_ring, head++, (AVR_CTX_BYPASS << 1) | (uint32_t)b);
+          AVR_DEC_RENORM(low, range);
           if (!b || j >= 30) break;
           j++;
         }
         while (j--) {
-          const int b = avr_dec_default(low, range, AVR_CTX_BYPASS);
-          avr_ring_post_r(head, tail_seen, AVR_CTX_BYPASS, b);
-          bins++;
+          const int b = avr_dec_reg(low, range, s_ms, byp, 0x60);
+          avr_ring_store(s_ring, head++, (AVR_CTX_BYPASS << 1) | (uint32_t)b);
+          AVR_DEC_RENORM(low, range);
         }
       }
     }
-    const int sgn = avr_dec_default(low, range, AVR_CTX_BYPASS);
-    avr_ring_post_r(head, tail_seen, AVR_CTX_BYPASS, sgn);
-    bins++;
+    const int sgn = avr_dec_reg(low, range, s_ms, byp, 0x60);
+    avr_ring_store(s_ring, head++, (AVR_CTX_BYPASS << 1) | (uint32_t)sgn);
+    AVR_DEC_RENORM(low, range);
   }
+  avr_s_st16(a_byp, byp.cell);
   g_dec.low = low; g_dec.range = range;
   g_dec.ring_head = head; g_dec.ring_tail_seen = tail_seen;
-  g_dec.bins += bins;
+  g_dec.bins += head - head0;
   return coeff_count;
 }
 
@@ -386,6 +536,7 @@ struct AvrDecPolicy {
 
 // ---- per-file / per-slice driver ---------------------------------------------------------------
 AVR_DEC_INL void avr_dec_file_begin(uint16_t* est, uint8_t* s0, uint8_t* s1) {   // chain thread only
+  g_dec.self = (uint64_t)avr_sp(&g_dec);
   g_dec.est = est; g_dec.store[0] = s0; g_dec.store[1] = s1; g_dec.cur = 0; g_dec.mb_w = 1;
   g_dec.ring_head = 0; g_dec.ring_tail_seen = 0; g_dec.ring_tail = 0;
 }
@@ -415,7 +566,7 @@ AVR_DEC_FN int avr_dec_slice(const AvrDecSlice& ds, const uint8_t* payloads, avr
 static void avr_decompress_file_host(const AvrFileDesc& fd, const AvrDecSlice* slices_all, const uint8_t* payloads,
                                      uint16_t* est, uint8_t* store0, uint8_t* store1, avr::MbInfo* row, const AvrTables* tab,
                                      uint8_t* out, uint32_t* out_len, uint32_t* out_bins, int* status) {
-  g_dec.hot = tab->hot;
+  g_dec.hot = tab->hot; avr_ms_fill();
   for (uint32_t i = 0; i < AVR_NUM_CTX_KEYS; i++) g_dec.est_def[i] = AVR_EST_INIT;
   avr_dec_file_begin(est, store0, store1);
   uint32_t uid = 0;

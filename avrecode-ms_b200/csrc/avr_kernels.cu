@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     uint32_t* dst = reinterpret_cast<uint32_t*>(&g_dec.hot);
     for (uint32_t i = tid; i < sizeof(AvrHotTabs) / 4; i += AVR_DEC_THREADS) dst[i] = src[i];
     for (uint32_t i = tid; i < AVR_NUM_CTX_KEYS; i += AVR_DEC_THREADS) g_dec.est_def[i] = AVR_EST_INIT;
-    for (uint32_t i = tid; i < AVR_RING; i += AVR_DEC_THREADS) g_dec.ring[i] = 0;
+    for (uint32_t i = tid; i < AVR_RING; i += AVR_DEC_THREADS) g_dec.ring[i] = AVR_RING_EMPTY;
+    for (uint32_t i = tid; i < 98; i += AVR_DEC_THREADS) { g_dec.ms[i].m = tab->hot.div.m[i]; g_dec.ms[i].s = tab->hot.div.s[i]; }
   }
   if (tid == 0) {
     uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
