@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <string>
+#include <thread>
 #include <vector>
 #include "../../include/avrecode_b200.h"
 #include "avr_api_internal.h"
@@ -45,12 +46,35 @@ struct AvrArena {
   void give(void* p, size_t n) { free_blocks.push_back({n, p}); cached += n; }
   void flush() { for (auto& b : free_blocks) cudaFree(b.second); free_blocks.clear(); cached = 0; }
 };
+// Page-locked host staging, cached the same way: D2H into pageable memory goes through the driver's own bounce
+// buffers at a third of the bandwidth, and a fresh std::vector of the payload size is zero-filled first.
+struct AvrPinned {
+  std::vector<std::pair<size_t, void*>> free_blocks;
+  void* take(size_t n, size_t* got) {
+    for (size_t i = 0; i < free_blocks.size(); i++)
+      if (free_blocks[i].first >= n) {
+        void* p = free_blocks[i].second; *got = free_blocks[i].first;
+        free_blocks.erase(free_blocks.begin() + i);
+        return p;
+      }
+    for (auto& b : free_blocks) cudaFreeHost(b.second);      // too small: one growing buffer per role is enough
+    free_blocks.clear();
+    void* p = nullptr;
+    n = (n + (n >> 2) + (1u << 20)) & ~(size_t)4095;
+    if (cudaHostAlloc(&p, n, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    *got = n;
+    return p;
+  }
+  void give(void* p, size_t n) { if (p) free_blocks.push_back({n, p}); }
+  void flush() { for (auto& b : free_blocks) cudaFreeHost(b.second); free_blocks.clear(); }
+};
 struct avr_context {
   int device;
   cudaStream_t stream;
   AvrTables* d_tab;
   cudaEvent_t ev[4];
   AvrArena arena;
+  AvrPinned pinned;
 };
 
 extern "C" int avr_context_create(int device, avr_context** out) {
@@ -76,7 +100,7 @@ extern "C" int avr_context_create(int device, avr_context** out) {
 extern "C" void avr_context_destroy(avr_context* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  c->arena.flush();
+  c->arena.flush(); c->pinned.flush();
   cudaFree(c->d_tab);
   for (auto& e : c->ev) cudaEventDestroy(e);
   cudaStreamDestroy(c->stream);
@@ -185,7 +209,7 @@ struct avr_cbatch {
   AvrDevBatch d;
   std::vector<uint32_t> file_slice_off;    // per file: first batch-global slice
   std::vector<uint32_t> h_len; std::vector<int> h_status; std::vector<uint64_t> h_off;
-  std::vector<uint8_t> h_out;
+  uint8_t* h_out = nullptr; size_t h_out_cap = 0;   // page-locked, from the context's cache
   uint64_t scratch_bytes = 0, pic_mbs = 0, chain_mbs = 0;
   bool have_pipe = false, have_chain = false;
   uint32_t create_launches = 0;           // kernels launched by avr_cbatch_create_files (parse, block gather)
@@ -350,8 +374,12 @@ extern "C" int avr_cbatch_fetch(avr_cbatch* b) {
     cudaMemcpyAsync(&total, d.out_total, sizeof total, cudaMemcpyDeviceToHost, st);
     CU(cudaStreamSynchronize(st));
     if (total > b->scratch_bytes) { avr_set_error("payload total %llu exceeds scratch", (unsigned long long)total); return AVR_E_OVERFLOW; }
-    b->h_out.resize(total);
-    if (total) cudaMemcpyAsync(b->h_out.data(), d.out, total, cudaMemcpyDeviceToHost, st);
+    if (total > b->h_out_cap) {
+      ctx->pinned.give(b->h_out, b->h_out_cap);
+      b->h_out = (uint8_t*)ctx->pinned.take(total, &b->h_out_cap);
+      if (!b->h_out) { b->h_out_cap = 0; avr_set_error("cudaHostAlloc(%llu) failed", (unsigned long long)total); return AVR_E_NOMEM; }
+    }
+    if (total) cudaMemcpyAsync(b->h_out, d.out, total, cudaMemcpyDeviceToHost, st);
   }
   cudaEventRecord(ctx->ev[1], st);
   CU(cudaStreamSynchronize(st));
@@ -367,7 +395,7 @@ extern "C" int avr_cbatch_payload(const avr_cbatch* b, int file, uint32_t slice,
   if (!b || !b->fetched || file < 0 || file >= b->d.nfiles) return AVR_E_ARG;
   uint32_t s = b->file_slice_off[file] + slice;
   if (s >= b->file_slice_off[file + 1]) return AVR_E_ARG;
-  *data = b->h_out.data() + b->h_off[s];
+  *data = b->h_out + b->h_off[s];
   *len = b->h_len[s];
   return AVR_OK;
 }
@@ -377,6 +405,7 @@ extern "C" void avr_cbatch_destroy(avr_cbatch* b) {
   if (!b) return;
   avr_cbatch_files_release(b);
   cudaSetDevice(b->ctx->device);
+  b->ctx->pinned.give(b->h_out, b->h_out_cap);
   b->mem.release();
   delete b;
 }
@@ -388,7 +417,7 @@ struct avr_dbatch {
   AvrDevDBatch d;
   std::vector<uint64_t> out_off; std::vector<uint32_t> out_cap;
   std::vector<uint32_t> h_len, h_bins; std::vector<int> h_status;
-  std::vector<uint8_t> h_out;
+  uint8_t* h_out = nullptr; size_t h_out_cap = 0;   // page-locked, from the context's cache
   uint64_t out_bytes = 0;
   avr_timing t;
   bool ran = false, fetched = false;
@@ -450,7 +479,24 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };
   up(d_fds, fds.data(), fds.size() * sizeof(AvrFileDesc));
   up(d_ds, ds.data(), ds.size() * sizeof(AvrDecSlice));
-  for (size_t i = 0; i < ds.size(); i++) up(d_pay + ds[i].payload_off, slices[i].payload, slices[i].payload_len);
+  {
+    // one page-locked staging buffer and one copy instead of a pageable copy per slice
+    size_t cap = 0;
+    uint8_t* stage = pay ? (uint8_t*)ctx->pinned.take(pay, &cap) : nullptr;
+    if (stage) {
+      const int nth = pay > (4u << 20) ? 8 : 1;
+      std::vector<std::thread> th;
+      for (int t = 0; t < nth; t++) th.emplace_back([&, t] {
+        for (size_t i = (size_t)t; i < ds.size(); i += (size_t)nth) if (slices[i].payload_len) memcpy(stage + ds[i].payload_off, slices[i].payload, slices[i].payload_len);
+      });
+      for (auto& t : th) t.join();
+      up(d_pay, stage, pay);
+      cudaStreamSynchronize(st);
+      ctx->pinned.give(stage, cap);
+    } else {
+      for (size_t i = 0; i < ds.size(); i++) up(d_pay + ds[i].payload_off, slices[i].payload, slices[i].payload_len);
+    }
+  }
   cudaEventRecord(ctx->ev[1], st);
   cudaError_t e = cudaStreamSynchronize(st);
   if (e != cudaSuccess) { avr_set_error("upload: %s", cudaGetErrorString(e)); return fail(AVR_E_CUDA); }
@@ -490,13 +536,18 @@ extern "C" int avr_dbatch_fetch(avr_dbatch* b) {
   AvrDevDBatch& d = b->d;
   cudaStream_t st = ctx->stream;
   const size_t ns = d.nslices;
-  b->h_len.resize(ns); b->h_bins.resize(ns); b->h_status.resize(ns); b->h_out.resize(b->out_bytes);
+  b->h_len.resize(ns); b->h_bins.resize(ns); b->h_status.resize(ns);
+  if (b->out_bytes > b->h_out_cap) {
+    ctx->pinned.give(b->h_out, b->h_out_cap);
+    b->h_out = (uint8_t*)ctx->pinned.take(b->out_bytes, &b->h_out_cap);
+    if (!b->h_out) { b->h_out_cap = 0; avr_set_error("cudaHostAlloc(%llu) failed", (unsigned long long)b->out_bytes); return AVR_E_NOMEM; }
+  }
   cudaEventRecord(ctx->ev[0], st);
   if (ns) {
     cudaMemcpyAsync(b->h_len.data(), d.out_len, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(b->h_bins.data(), d.out_bins, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost, st);
     cudaMemcpyAsync(b->h_status.data(), d.status, ns * sizeof(int), cudaMemcpyDeviceToHost, st);
-    cudaMemcpyAsync(b->h_out.data(), d.out, b->out_bytes, cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(b->h_out, d.out, b->out_bytes, cudaMemcpyDeviceToHost, st);
   }
   cudaEventRecord(ctx->ev[1], st);
   CU(cudaStreamSynchronize(st));
@@ -513,7 +564,7 @@ extern "C" int avr_dbatch_fetch(avr_dbatch* b) {
 
 extern "C" int avr_dbatch_slice(const avr_dbatch* b, uint32_t slice, const uint8_t** data, uint32_t* len, uint32_t* bins) {
   if (!b || !b->fetched || slice >= b->d.nslices) return AVR_E_ARG;
-  if (data) *data = b->h_out.data() + b->out_off[slice];
+  if (data) *data = b->h_out + b->out_off[slice];
   if (len) *len = b->h_len[slice];
   if (bins) *bins = b->h_bins[slice];
   return AVR_OK;
@@ -522,6 +573,7 @@ extern "C" void avr_dbatch_timing(const avr_dbatch* b, avr_timing* t) { if (b &&
 extern "C" void avr_dbatch_destroy(avr_dbatch* b) {
   if (!b) return;
   cudaSetDevice(b->ctx->device);
+  b->ctx->pinned.give(b->h_out, b->h_out_cap);
   b->mem.release();
   delete b;
 }

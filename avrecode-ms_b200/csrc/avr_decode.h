@@ -20,6 +20,7 @@
 #pragma once
 #include <stddef.h>
 #include "avr_bodies.h"
+#include "avr_mem.h"
 
 #define AVR_RING_LOG 10
 #define AVR_RING (1u << AVR_RING_LOG)
@@ -284,32 +285,8 @@ AVR_DEC_FN int avr_dec_terminate() {
   return sym;
 }
 
-// ---- address-space explicit accessors for the residual-block loops -------------------------------
-// On the device: ld/st.shared with a 32-bit shared-window address and ld/st.global.  With plain C++
-// accesses ptxas re-derived the shared window base from SR_CgaCtaId inside the loops (an S2R per bin)
-// and used generic LD/ST with a per-iteration descriptor set-up for the estimator pool
-// (tools/sass_model.py on the v6 build).  On the host: plain memory.
-#if defined(__CUDA_ARCH__)
-typedef uint32_t avr_sptr;
-AVR_DEC_INL avr_sptr avr_sp(const void* p) { return (avr_sptr)__cvta_generic_to_shared(p); }
-AVR_DEC_INL uint32_t avr_s_ld16(avr_sptr a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a) : "memory"); return v; }
-AVR_DEC_INL void avr_s_st16(avr_sptr a, uint32_t v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"((uint16_t)v) : "memory"); }
-AVR_DEC_INL void avr_s_st32(avr_sptr a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
-AVR_DEC_INL void avr_s_ld_ms(avr_sptr a, uint64_t& m, uint32_t& sh) {     // read-only table: free to schedule
-  uint64_t t; asm("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(m), "=l"(t) : "r"(a)); sh = (uint32_t)t;
-}
-AVR_DEC_INL uint32_t avr_g_ld16(const uint16_t* p) { uint16_t v; asm volatile("ld.global.u16 %0, [%1];" : "=h"(v) : "l"(p) : "memory"); return v; }
-AVR_DEC_INL void avr_g_st16(uint16_t* p, uint32_t v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(p), "h"((uint16_t)v) : "memory"); }
-#else
-typedef uintptr_t avr_sptr;
-AVR_DEC_INL avr_sptr avr_sp(const void* p) { return (avr_sptr)p; }
-AVR_DEC_INL uint32_t avr_s_ld16(avr_sptr a) { return *reinterpret_cast<const uint16_t*>(a); }
-AVR_DEC_INL void avr_s_st16(avr_sptr a, uint32_t v) { *reinterpret_cast<uint16_t*>(a) = (uint16_t)v; }
-AVR_DEC_INL void avr_s_st32(avr_sptr a, uint32_t v) { *reinterpret_cast<uint32_t*>(a) = v; }
-AVR_DEC_INL void avr_s_ld_ms(avr_sptr a, uint64_t& m, uint32_t& sh) { const AvrMs* e = reinterpret_cast<const AvrMs*>(a); m = e->m; sh = (uint32_t)e->s; }
-AVR_DEC_INL uint32_t avr_g_ld16(const uint16_t* p) { return *p; }
-AVR_DEC_INL void avr_g_st16(uint16_t* p, uint32_t v) { *p = (uint16_t)v; }
-#endif
+// address-space explicit accessors: avr_mem.h
+AVR_DEC_INL void avr_s_ld_ms(avr_sptr a, uint64_t& m, uint32_t& sh) { uint64_t t; avr_s_ld_2x64_ro(a, m, t); sh = (uint32_t)t; }
 AVR_DEC_INL void avr_ms_fill() {     // chain thread, once per file
   for (uint32_t t = 0; t < 98; t++) { g_dec.ms[t].m = g_dec.hot.div.m[t]; g_dec.ms[t].s = g_dec.hot.div.s[t]; }
 }

@@ -86,8 +86,7 @@ __global__ void __launch_bounds__(32) avr_k_parse(const AvrParseSlice* ps, uint3
   const uint32_t s = blockIdx.x, lane = threadIdx.x;
   if (s >= n) return;
   const AvrParseSlice& p = ps[s];
-  for (uint32_t i = lane; i < 256; i += 32) g_par.range_lps[i] = tab->hot.range_lps[i];
-  for (uint32_t i = lane; i < 64; i += 32) g_par.trans_lps[i] = tab->hot.trans_lps[i];
+  avr_par_tables(tab, (int)lane, 32);
   avr_cabac_init_states(g_par.st, tab, p.sp.slice_type == avr::SLICE_I, p.sp.cabac_init_idc, p.sp.slice_qp, (int)lane, 32);
   __syncwarp();
   if (lane == 0) avr_parse_slice(p, raw, bins_pool, blk_pool, row_pool + row_off[s], &res[s]);

@@ -10,7 +10,9 @@
 //
 // Include only from avr_kernels.cu and tests/host_emul.cpp.
 #pragma once
+#include <stddef.h>
 #include "avr_bodies.h"
+#include "avr_mem.h"
 
 // One coded slice to parse.
 struct AvrParseSlice {
@@ -31,6 +33,8 @@ struct AvrParseResult {
 };
 
 struct AvrParShared {
+  uint64_t lut[64];                    // per pStateIdx: rangeTabLPS row (4 bytes) | transIdxLPS << 32, one load per decision
+  uint64_t self;                       // shared-window address of this object, read back as an opaque value (avr_decode.h avr_sbase)
   uint8_t st[1024];
   uint8_t range_lps[256];              // [pStateIdx][qRangeIdx]; read as one 32-bit row per state
   uint8_t trans_lps[64];
@@ -44,8 +48,8 @@ struct AvrParShared {
   AvrBlock* blocks; uint32_t nblk, blk_cap;
   uint32_t emitted, frame, mb_addr; int mb_w;
   int cat, n, max_coeff, is_dc;
-  int in_sigmap, expect_eob;
 };
+#define AVR_P_OFF(member) ((avr_sptr)offsetof(AvrParShared, member))
 
 #if defined(__CUDACC__)
 __shared__ AvrParShared g_par;
@@ -58,6 +62,18 @@ static AvrParShared g_par;
 #define AVR_PAR_INL static inline
 #define AVR_PAR_M inline
 #endif
+
+// tables of the engine; lane/nlanes split the work when a warp initialises them
+AVR_PAR_INL void avr_par_tables(const AvrTables* tab, int lane, int nlanes) {
+  for (int i = lane; i < 256; i += nlanes) g_par.range_lps[i] = tab->hot.range_lps[i];
+  for (int i = lane; i < 64; i += nlanes) {
+    g_par.trans_lps[i] = tab->hot.trans_lps[i];
+    uint64_t row = 0;
+    for (int q = 0; q < 4; q++) row |= (uint64_t)tab->hot.range_lps[(i << 2) | q] << (8 * q);
+    g_par.lut[i] = row | ((uint64_t)tab->hot.trans_lps[i] << 32);
+  }
+  if (lane == 0) g_par.self = (uint64_t)avr_sp(&g_par);
+}
 
 // Engine registers: live in g_par between the parser's single-bin calls, in registers across a residual block.
 struct AvrParRegs { uint32_t val, range, nextw, pos, nb; int nvalid; };
@@ -160,33 +176,85 @@ AVR_PAR_FN int avr_par_terminate() {
 }
 
 // ---- one residual block (h264_cabac.c:1583-1780; recorder: Recorder::begin_sub_mb / sigmap in avr_record.h) ----
-// Engine registers stay in registers for the whole block; the block record is written once.
-AVR_PAR_FN int avr_par_residual_block(int cat, int n, int max_coeff, int is_dc, int sig_base, int last_base, int abs_base) {
-  AvrParRegs r; avr_par_load(r);
-  const uint32_t bin_start = g_par.file_bin_base + r.nb;
+// Engine and recorder cursors stay in registers for the whole block; the block record is written once.
+// State byte and table row of the NEXT significance context are requested while the current bin is decided
+// (the context sequence of the map does not depend on the bins, only its length does).
+struct AvrParCtx { uint32_t s; uint64_t lut; };          // state byte + table entry of its pStateIdx
+AVR_PAR_INL void avr_par_ctx_load(avr_sptr s_st, avr_sptr s_lut, uint32_t ctx, AvrParCtx& c) {
+  c.s = avr_s_ld8(s_st + ctx);
+  c.lut = avr_s_ld64_ro(s_lut + ((c.s >> 1) << 3));
+}
+// DecodeDecision with the state already in registers; returns the bin, ns = new state byte
+AVR_PAR_INL int avr_par_decide(AvrParRegs& r, const AvrParCtx& c, uint32_t& ns) {
+  const uint32_t s = c.s, row = (uint32_t)c.lut, tl = (uint32_t)(c.lut >> 32);
+  const uint32_t lps = (row >> ((r.range >> 3) & 24)) & 0xFF;
+  const uint32_t rmps = r.range - lps;
+  const uint32_t scaled = rmps << 23;
+  const bool is_lps = r.val >= scaled;
+  const uint32_t ns_lps = (tl << 1) | ((s & 1) ^ (uint32_t)(s < 2));   // pStateIdx 0: valMPS flips
+  const uint32_t ns_mps = s < 124 ? s + 2 : s;
+  ns = is_lps ? ns_lps : ns_mps;
+  r.val -= is_lps ? scaled : 0u;
+  const uint32_t range = is_lps ? lps : rmps;
+  const int sh = AVR_CLZ32(range) - 23;                  // 0 when range >= 256
+  r.range = range << sh; r.val <<= sh; r.nvalid -= sh;
+  avr_par_refill(r);
+  return (int)((s & 1) ^ (uint32_t)is_lps);
+}
+AVR_PAR_INL void avr_par_put_r(uint16_t* bins, uint32_t cap_m1, uint32_t& nb, uint32_t rec) {
+  bins[nb < cap_m1 ? nb : cap_m1] = (uint16_t)rec;       // past the capacity: keep counting, status says overflow
+  nb++;
+}
+
+template <bool IS64>
+AVR_PAR_INL int avr_par_sigmap(AvrParRegs& r, avr_sptr s_st, avr_sptr s_lut, uint16_t* bins, uint32_t cap_m1, int max_coeff,
+                               int sig_base, int last_base, int* last_out) {
   const int coefs = max_coeff - 1;
-  int coeff_count = 0, last;
-  for (last = 0; last < coefs; last++) {
-    int sig_ctx = sig_base + last, last_ctx = last_base + last;
-    if (max_coeff == 64) {
-      sig_ctx = sig_base + avr_sig8x8_off(last);
-      last_ctx = last_base + (last == 0 ? 0 : last < 16 ? 1 : last < 32 ? 2 : last < 40 ? 3 : last < 48 ? 4 : last < 52 ? 5 : last < 56 ? 6 : last < 60 ? 7 : 8);
-    }
-    const int sig = avr_par_decision(r, sig_ctx);
-    avr_par_put(r, AVR_BIN(sig, sig_ctx, AVR_KIND_SIG_MAP));
+  int coeff_count = 0, last = 0;
+  uint32_t cs = (uint32_t)(sig_base + (IS64 ? avr_sig8x8_off(0) : 0));
+  AvrParCtx c; avr_par_ctx_load(s_st, s_lut, cs, c);
+  for (;;) {
+    const int nlast = last + 1;
+    const uint32_t ncs = (uint32_t)(sig_base + (IS64 ? avr_sig8x8_off(nlast & 63) : nlast));   // a valid state index even past the end
+    const uint32_t cl = (uint32_t)(last_base + (!IS64 ? last : last == 0 ? 0 : last < 16 ? 1 : last < 32 ? 2 : last < 40 ? 3 : last < 48 ? 4 : last < 52 ? 5 : last < 56 ? 6 : last < 60 ? 7 : 8));
+    AvrParCtx cn, cq; avr_par_ctx_load(s_st, s_lut, ncs, cn); avr_par_ctx_load(s_st, s_lut, cl, cq);
+    uint32_t ns;
+    const int sig = avr_par_decide(r, c, ns);
+    avr_s_st8(s_st + cs, ns);
+    avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(sig, cs, AVR_KIND_SIG_MAP));
+    if (IS64 && ncs == cs) { cn.s = ns; cn.lut = avr_s_ld64_ro(s_lut + ((ns >> 1) << 3)); }   // 8x8 offsets repeat: what was read is stale
     if (sig) {
       coeff_count++;
-      const int eob = avr_par_decision(r, last_ctx);
-      avr_par_put(r, AVR_BIN(eob, last_ctx, AVR_KIND_SIG_EOB));
+      uint32_t nq;
+      const int eob = avr_par_decide(r, cq, nq);
+      avr_s_st8(s_st + cl, nq);
+      avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(eob, cl, AVR_KIND_SIG_EOB));
       if (eob) { last = max_coeff; break; }
     }
+    last = nlast;
+    if (nlast >= coefs) break;
+    c = cn; cs = ncs;
   }
-  const uint32_t map_bins = g_par.file_bin_base + r.nb - bin_start;
+  *last_out = last;
+  return coeff_count;
+}
+
+AVR_PAR_FN int avr_par_residual_block(int cat, int n, int max_coeff, int is_dc, int sig_base, int last_base, int abs_base) {
+  AvrParRegs r; avr_par_load(r);
+  uint16_t* const bins = g_par.bins;
+  const uint32_t cap_m1 = g_par.bin_cap - 1;
+  const avr_sptr s_base = (avr_sptr)g_par.self, s_st = s_base + AVR_P_OFF(st), s_lut = s_base + AVR_P_OFF(lut);
+  const uint32_t nb0 = r.nb;
+  int coeff_count = 0, last = 0;
+  if (max_coeff > 1)
+    coeff_count = max_coeff == 64 ? avr_par_sigmap<true>(r, s_st, s_lut, bins, cap_m1, max_coeff, sig_base, last_base, &last)
+                                  : avr_par_sigmap<false>(r, s_st, s_lut, bins, cap_m1, max_coeff, sig_base, last_base, &last);
+  const uint32_t map_bins = r.nb - nb0;
   uint32_t emitted = (uint32_t)avr_nz_bits(max_coeff) + map_bins - (uint32_t)coeff_count;   // EOB bins are inferred, not coded
   if (last == max_coeff - 1) coeff_count++;
   if (g_par.nblk < g_par.blk_cap) {
     AvrBlock b;
-    b.bin_start = bin_start; b.mb_addr = g_par.mb_addr; b.frame = g_par.frame;
+    b.bin_start = g_par.file_bin_base + nb0; b.mb_addr = g_par.mb_addr; b.frame = g_par.frame;
     b.n = (uint8_t)n; b.cat_flags = (uint8_t)(cat | (is_dc << 4)); b.max_coeff = (uint8_t)max_coeff;
     b.nbins = (uint8_t)map_bins;
     g_par.blocks[g_par.nblk] = b;
@@ -197,34 +265,38 @@ AVR_PAR_FN int avr_par_residual_block(int cat, int n, int max_coeff, int is_dc, 
   int node_ctx = 0;
   const int gt1_max = cat == 3 ? 8 : 9;
   for (int c = coeff_count; c > 0; c--) {
-    const int ctx1 = abs_base + (node_ctx < 4 ? node_ctx + 1 : 0);
-    const int b0 = avr_par_decision(r, ctx1);
-    avr_par_put(r, AVR_BIN(b0, ctx1, AVR_KIND_DEFAULT));
+    const uint32_t ctx1 = (uint32_t)(abs_base + (node_ctx < 4 ? node_ctx + 1 : 0));
+    const uint32_t ctx2 = (uint32_t)(abs_base + (node_ctx < 4 ? 5 : (node_ctx + 2 > gt1_max ? gt1_max : node_ctx + 2)));
+    AvrParCtx c1, c2; avr_par_ctx_load(s_st, s_lut, ctx1, c1); avr_par_ctx_load(s_st, s_lut, ctx2, c2);   // never the same state byte
+    uint32_t ns;
+    const int b0 = avr_par_decide(r, c1, ns);
+    avr_s_st8(s_st + ctx1, ns);
+    avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(b0, ctx1, AVR_KIND_DEFAULT));
     if (b0 == 0) {
       node_ctx = node_ctx < 3 ? node_ctx + 1 : node_ctx;
     } else {
-      const int gt1 = node_ctx < 4 ? 5 : (node_ctx + 2 > gt1_max ? gt1_max : node_ctx + 2);
-      const int ctx2 = abs_base + gt1;
       node_ctx = node_ctx < 4 ? 4 : (node_ctx < 7 ? node_ctx + 1 : 7);
       int coeff_abs = 2;
-      while (coeff_abs < 15) {
-        const int b = avr_par_decision(r, ctx2);
-        avr_par_put(r, AVR_BIN(b, ctx2, AVR_KIND_DEFAULT));
+      while (coeff_abs < 15) {                           // the ctx2 state stays in registers across its run
+        const int b = avr_par_decide(r, c2, ns);
+        c2.s = ns; c2.lut = avr_s_ld64_ro(s_lut + ((ns >> 1) << 3));
+        avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(b, ctx2, AVR_KIND_DEFAULT));
         if (!b) break;
         coeff_abs++;
       }
+      avr_s_st8(s_st + ctx2, c2.s);
       if (coeff_abs >= 15) {
         int j = 0;
         for (;;) {
           const int b = avr_par_bypass_r(r);
-          avr_par_put(r, AVR_BIN(b, AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+          avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(b, AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
           if (!b || j >= 30) break;
           j++;
         }
-        while (j--) avr_par_put(r, AVR_BIN(avr_par_bypass_r(r), AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+        while (j--) avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(avr_par_bypass_r(r), AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
       }
     }
-    avr_par_put(r, AVR_BIN(avr_par_bypass_r(r), AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
+    avr_par_put_r(bins, cap_m1, r.nb, AVR_BIN(avr_par_bypass_r(r), AVR_CTX_BYPASS, AVR_KIND_DEFAULT));
   }
   emitted += r.nb - lvl_start;
   g_par.emitted += emitted;

@@ -202,7 +202,7 @@ static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& 
   int rc = avr::scan_annexb(data.data(), data.size(), &scan, &coded);
   if (rc) { printf("scan rc=%d\n", rc); return 1; }
   std::vector<uint16_t> bins; std::vector<AvrBlock> blocks;
-  memcpy(g_par.range_lps, tab.hot.range_lps, 256); memcpy(g_par.trans_lps, tab.hot.trans_lps, 64);
+  avr_par_tables(&tab, 0, 1);
   std::vector<uint8_t> raw(data); raw.resize(raw.size() + 16);
   uint64_t emitted = 0;
   for (const avr::ScanSlice& c : coded) {
