@@ -7,6 +7,7 @@
 #include <string.h>
 #include <string>
 #include <thread>
+#include <algorithm>
 #include <vector>
 #include "../../include/avrecode_b200.h"
 #include "avr_api_internal.h"
@@ -203,6 +204,12 @@ struct DevMem {
 static float ev_ms(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
 
 // ---- compress batch ---------------------------------------------------------------------------
+static std::vector<uint32_t> code_order_of(const std::vector<AvrBatchSlice>& bsl) {
+  std::vector<uint32_t> o(bsl.size());
+  for (uint32_t i = 0; i < o.size(); i++) o[i] = i;
+  std::stable_sort(o.begin(), o.end(), [&](uint32_t a, uint32_t b) { return bsl[a].bin_end - bsl[a].bin_start > bsl[b].bin_end - bsl[b].bin_start; });
+  return o;
+}
 struct avr_cbatch {
   avr_context* ctx;
   DevMem mem;
@@ -283,6 +290,9 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
       (rc = m.alloc(&d.out_off, bsl.size())) || (rc = m.alloc(&d.out_total, 1)) || (rc = m.alloc(&d.out, scratch)))
     return fail(rc);
   d.fds = d_fds; d.bins = d_bins; d.blocks = d_blocks; d.slices = d_sl; d.bslices = d_bsl; d.frames = d_frames;
+  uint32_t* d_order; if ((rc = m.alloc(&d_order, bsl.size()))) return fail(rc);
+  d.code_order = d_order;
+  const std::vector<uint32_t> order = code_order_of(bsl);
   d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
   // upload (timed: this is the H2D leg of the e2e number)
   cudaStream_t st = ctx->stream;
@@ -298,6 +308,7 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
   }
   up(d_sl, sl.data(), sl.size() * sizeof(AvrSlice));
   up(d_bsl, bsl.data(), bsl.size() * sizeof(AvrBatchSlice));
+  up(d_order, order.data(), order.size() * sizeof(uint32_t));
   up(b->d_scratch_off, soff.data(), soff.size() * sizeof(uint64_t));
   up(b->d_scratch_cap, scap.data(), scap.size() * sizeof(uint32_t));
   cudaEventRecord(ctx->ev[1], st);
@@ -646,9 +657,14 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   auto fail = [&](int r) { tmp.release(); m.release(); delete b; delete bf; return r; };
   const uint32_t ns = (uint32_t)ps.size();
   uint8_t* d_raw; uint16_t* d_bins; AvrBlock* d_blkpool; avr::MbInfo* d_rows; uint64_t* d_row_off; AvrParseSlice* d_ps; AvrParseResult* d_res;
+  uint32_t* d_order;
+  std::vector<uint32_t> order(ps.size());
+  for (uint32_t i = 0; i < order.size(); i++) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return ps[a].size > ps[b].size; });
   int rc;
   if ((rc = tmp.alloc(&d_raw, raw_bytes + 64)) || (rc = m.alloc(&d_bins, bin_pool)) || (rc = tmp.alloc(&d_blkpool, blk_pool)) ||
-      (rc = tmp.alloc(&d_rows, rows)) || (rc = tmp.alloc(&d_row_off, ns)) || (rc = tmp.alloc(&d_ps, ns)) || (rc = tmp.alloc(&d_res, ns)))
+      (rc = tmp.alloc(&d_rows, rows)) || (rc = tmp.alloc(&d_row_off, ns)) || (rc = tmp.alloc(&d_ps, ns)) || (rc = tmp.alloc(&d_res, ns)) ||
+      (rc = tmp.alloc(&d_order, ns)))
     return fail(rc);
   avr_trace("cf: pool alloc");
   cudaStream_t st = ctx->stream;
@@ -666,8 +682,9 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
     if (!file_status[f] && lens[f]) { cudaMemcpyAsync(d_raw + raw_base[f], files[f], lens[f], cudaMemcpyHostToDevice, st); h2d += lens[f]; }
   cudaMemcpyAsync(d_ps, ps.data(), ns * sizeof(AvrParseSlice), cudaMemcpyHostToDevice, st); h2d += ns * sizeof(AvrParseSlice);
   cudaMemcpyAsync(d_row_off, row_off.data(), ns * sizeof(uint64_t), cudaMemcpyHostToDevice, st); h2d += ns * 8;
+  cudaMemcpyAsync(d_order, order.data(), ns * sizeof(uint32_t), cudaMemcpyHostToDevice, st); h2d += ns * 4;
   cudaEventRecord(ctx->ev[1], st);
-  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, st);
+  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, d_order, st);
   cudaEventRecord(ctx->ev[2], st);
   if (rc) { avr_set_error("parse launch: %s", cudaGetErrorString((cudaError_t)rc)); return fail(AVR_E_CUDA); }
   std::vector<AvrParseResult> res(ns);
@@ -725,10 +742,14 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
     return fail(rc);
   avr_trace("cf: layout+alloc2");
   d.fds = d_fds; d.blocks = d_blocks; d.bslices = d_bsl; d.frames = d_frames; d.slices = nullptr;
+  uint32_t* d_corder; if ((rc = m.alloc(&d_corder, bsl.size()))) return fail(rc);
+  d.code_order = d_corder;
+  const std::vector<uint32_t> corder = code_order_of(bsl);
   d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
   cudaEventRecord(ctx->ev[0], st);
   auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };
   up(d_fds, fds.data(), fds.size() * sizeof(AvrFileDesc)); up(d_bsl, bsl.data(), bsl.size() * sizeof(AvrBatchSlice));
+  up(d_corder, corder.data(), corder.size() * sizeof(uint32_t));
   up(d_frames, frames.data(), frames.size() * sizeof(AvrFrame)); up(d_cnt, blk_cnt.data(), ns * 4); up(d_dst, blk_dst.data(), ns * 4);
   up(b->d_scratch_off, soff.data(), soff.size() * 8); up(b->d_scratch_cap, scap.data(), scap.size() * 4);
   rc = avr_launch_gather_blocks(d_blkpool, d_ps, d_cnt, d_dst, d_blocks, ns, st);

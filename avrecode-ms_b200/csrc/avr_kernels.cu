@@ -78,13 +78,18 @@ __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
   }
 }
 
+__global__ void __launch_bounds__(128) avr_k_patch_tails(const AvrParseSlice* ps, uint32_t n, uint8_t* raw) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) avr_body_patch_tail(ps[s], raw);
+}
 // Compress-side parse on the device (avr_parse.h): one warp per coded slice, lane 0 walks the slice,
 // all lanes initialise the CABAC states and tables.
 __global__ void __launch_bounds__(32) avr_k_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool,
                                                   AvrBlock* blk_pool, avr::MbInfo* row_pool, const uint64_t* row_off,
-                                                  const AvrTables* tab, AvrParseResult* res) {
-  const uint32_t s = blockIdx.x, lane = threadIdx.x;
-  if (s >= n) return;
+                                                  const AvrTables* tab, AvrParseResult* res, const uint32_t* order) {
+  const uint32_t lane = threadIdx.x;
+  if (blockIdx.x >= n) return;
+  const uint32_t s = order[blockIdx.x];        // longest payload first: the grid runs in several waves (32 slices per SM at a time)
   const AvrParseSlice& p = ps[s];
   avr_par_tables(tab, (int)lane, 32);
   avr_cabac_init_states(g_par.st, tab, p.sp.slice_type == avr::SLICE_I, p.sp.cabac_init_idc, p.sp.slice_qp, (int)lane, 32);
@@ -210,9 +215,11 @@ __global__ void __launch_bounds__(256) avr_k_estimate(const uint32_t* sorted, co
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) avr_body_estimate(i, sorted, idx, head, P, fn, prob);
 }
-// thread per slice: the one inherently serial pass.  The exact-division table is staged in shared
-// memory (indexed by the data-dependent total, different in every lane).
-__global__ void __launch_bounds__(32) avr_k_code(AvrPipe a) {
+// One slice per warp, coded by lane 0: the one inherently serial pass.  (One slice per LANE made every step of the
+// warp pay for the renormalisation of whichever lane needed it -- about one symbol in nine per lane, so nearly every
+// step of 32 -- and for the longest slice of the 32.)  The exact-division table is staged in shared memory by the warp.
+// Launch order: longest slice first.
+__global__ void __launch_bounds__(32) avr_k_code(AvrPipe a, const uint32_t* order) {
   __shared__ AvrDivTab dt;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(&a.tab->hot.div);
@@ -220,8 +227,8 @@ __global__ void __launch_bounds__(32) avr_k_code(AvrPipe a) {
     for (uint32_t i = threadIdx.x; i < sizeof(AvrDivTab) / 4; i += 32) dst[i] = src[i];
   }
   __syncwarp();
-  uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < a.nslices) avr_body_code(a, s, &dt);
+  if (blockIdx.x >= a.nslices || threadIdx.x != 0) return;
+  avr_body_code(a, order ? order[blockIdx.x] : blockIdx.x, &dt);
 }
 
 size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bit) {
@@ -270,16 +277,18 @@ int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* lau
   AVR_CK(cub::DeviceScan::InclusiveScan(b.cub_tmp, tmp, fe, b.fn, AvrHalfSegOp(), (int)n, st)); nl += 2;
   avr_k_estimate<<<(n + 255) / 256, 256, 0, st>>>(b.keys_b, b.idx_b, b.head, b.psum, b.fn, b.prob, n); nl++;
   if (coder_begin) cudaEventRecord(coder_begin, st);
-  avr_k_code<<<(b.nslices + 31) / 32, 32, 0, st>>>(a); nl++;
+  avr_k_code<<<b.nslices, 32, 0, st>>>(a, b.code_order); nl++;
   if (coder_end) cudaEventRecord(coder_end, st);
   if (launches) *launches = nl;
   return (int)cudaGetLastError();
 }
 
-int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
-                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, cudaStream_t st) {
+int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
+                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, const uint32_t* order,
+                     cudaStream_t st) {
   if (n == 0) return 0;
-  avr_k_parse<<<n, 32, 0, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res);
+  avr_k_patch_tails<<<(n + 127) / 128, 128, 0, st>>>(ps, n, raw);
+  avr_k_parse<<<n, 32, 0, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
   return (int)cudaGetLastError();
 }
 int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,

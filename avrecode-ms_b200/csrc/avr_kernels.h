@@ -16,6 +16,7 @@ struct AvrDevBatch {
   const AvrBlock* blocks;
   const AvrSlice* slices;          // file-local slice table (chain kernel)
   const AvrBatchSlice* bslices;    // batch-global slice table (pipeline)
+  const uint32_t* code_order;      // slices by descending bin count (pass D launch order), or null
   const AvrFrame* frames;
   const AvrTables* tab;
   // chain kernel state
@@ -55,7 +56,7 @@ size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bi
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st);
 int avr_launch_compact(const uint8_t* scratch, const uint64_t* scratch_off, const uint32_t* len, uint64_t* out_off,
                        uint64_t* total, uint8_t* out, uint32_t n, cudaStream_t st);
-int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
-                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, cudaStream_t st);
+int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
+                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, const uint32_t* order, cudaStream_t st);
 int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,
                              AvrBlock* dst, uint32_t n, cudaStream_t st);

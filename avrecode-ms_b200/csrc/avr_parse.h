@@ -32,6 +32,11 @@ struct AvrParseResult {
   int status;
 };
 
+// before the parse: the bytes that follow a payload in the pool become the bytes libavcodec's buffer holds there
+static AVR_HD void avr_body_patch_tail(const AvrParseSlice& ps, uint8_t* raw) {
+  for (int k = 0; k < 4; k++) raw[ps.raw_off + ps.size + (uint32_t)k] = ps.tail[k];
+}
+
 struct AvrParShared {
   uint64_t lut[64];                    // per pStateIdx: rangeTabLPS row (4 bytes) | transIdxLPS << 32, one load per decision
   uint64_t self;                       // shared-window address of this object, read back as an opaque value (avr_decode.h avr_sbase)
@@ -42,7 +47,7 @@ struct AvrParShared {
   // below are read-ahead; "offset >= range" is val >= range << 23 and renormalisation is a plain shift
   uint32_t val, range, nextw;          // nextw = the 16 bits that follow the valid ones (loaded one refill ahead)
   int nvalid;                          // valid bits in val, from the top (>= 17 between bins)
-  const uint8_t* in; uint32_t pos, size; uint32_t tail;
+  const uint8_t* in; uint32_t pos, size;
   // recorder (avr_record.h Recorder)
   uint16_t* bins; uint32_t nb, bin_cap, file_bin_base;
   AvrBlock* blocks; uint32_t nblk, blk_cap;
@@ -76,35 +81,43 @@ AVR_PAR_INL void avr_par_tables(const AvrTables* tab, int lane, int nlanes) {
 }
 
 // Engine registers: live in g_par between the parser's single-bin calls, in registers across a residual block.
-struct AvrParRegs { uint32_t val, range, nextw, pos, nb; int nvalid; };
+struct AvrParRegs { uint32_t val, range, nextw, pos, nb, lim; int nvalid; const uint8_t* in; };
 AVR_PAR_INL void avr_par_load(AvrParRegs& r) {
   r.val = g_par.val; r.range = g_par.range; r.nextw = g_par.nextw; r.pos = g_par.pos; r.nb = g_par.nb; r.nvalid = g_par.nvalid;
+  r.in = g_par.in; r.lim = g_par.size + 6;
 }
 AVR_PAR_INL void avr_par_store(const AvrParRegs& r) {
   g_par.val = r.val; g_par.range = r.range; g_par.nextw = r.nextw; g_par.pos = r.pos; g_par.nb = r.nb; g_par.nvalid = r.nvalid;
 }
-// two stream bytes at pos, big-endian; past `size` come the bytes libavcodec's buffer holds there, then zeros
-AVR_PAR_INL uint32_t avr_par_word(uint32_t pos) {
-  if (pos + 1 < g_par.size) return ((uint32_t)g_par.in[pos] << 8) | g_par.in[pos + 1];
-  uint32_t w = 0;
-  for (uint32_t k = 0; k < 2; k++) {
-    const uint32_t q = pos + k;
-    const uint32_t b = q < g_par.size ? g_par.in[q] : q - g_par.size < 4 ? (g_par.tail >> (8 * (q - g_par.size))) & 0xFF : 0u;
-    w = (w << 8) | b;
-  }
-  return w;
+// Two stream bytes at pos, big-endian.  The four bytes after the payload have been overwritten in the pool with what
+// libavcodec's unescaped buffer holds there (avr_body_patch_tail), so the reader needs no end-of-payload cases; reads are
+// clamped a few bytes past the end (a broken stream must not walk out of the pool; a valid one never gets there).
+AVR_PAR_INL uint32_t avr_par_word(const AvrParRegs& r, uint32_t pos) {
+  const uint32_t p = pos < r.lim ? pos : r.lim;
+  return ((uint32_t)r.in[p] << 8) | r.in[p + 1];
+}
+// Rare (once per ~20 bins) and deliberately a call: inlined, ptxas predicates the body into every decision and
+// schedules the state prefetches behind the whole decision chain (tools/sass_model.py: 115 -> 220 cycles per bin).
+struct AvrParFill { uint32_t val, nextw, pos; };
+AVR_PAR_FN AvrParFill avr_par_refill_slow(uint32_t val, uint32_t nextw, uint32_t pos, int nvalid, uint32_t lim, const uint8_t* in) {
+  AvrParFill f;
+  f.val = val | (nextw << (16 - nvalid));
+  f.pos = pos + 2;
+  const uint32_t p = f.pos < lim ? f.pos : lim;
+  f.nextw = ((uint32_t)in[p] << 8) | in[p + 1];          // used one refill later: its latency stays off the bin chain
+  return f;
 }
 AVR_PAR_INL void avr_par_refill(AvrParRegs& r) {
   if (r.nvalid <= 16) {
-    r.val |= r.nextw << (16 - r.nvalid);
+    const AvrParFill f = avr_par_refill_slow(r.val, r.nextw, r.pos, r.nvalid, r.lim, r.in);
+    r.val = f.val; r.nextw = f.nextw; r.pos = f.pos;
     r.nvalid += 16;
-    r.pos += 2;
-    r.nextw = avr_par_word(r.pos);      // used one refill later: its latency stays off the bin chain
   }
 }
 AVR_PAR_INL void avr_par_engine_init(AvrParRegs& r) {
-  r.val = (avr_par_word(0) << 16) | avr_par_word(2);
-  r.nvalid = 32; r.pos = 4; r.nextw = avr_par_word(4);
+  r.in = g_par.in; r.lim = g_par.size + 6;
+  r.val = (avr_par_word(r, 0) << 16) | avr_par_word(r, 2);
+  r.nvalid = 32; r.pos = 4; r.nextw = avr_par_word(r, 4);
   r.range = 510; r.nb = 0;
 }
 AVR_PAR_INL void avr_par_put(AvrParRegs& r, uint32_t rec) {
@@ -323,7 +336,6 @@ struct AvrParsePolicy {
 AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
                                 avr::MbInfo* row, AvrParseResult* res) {
   g_par.in = raw + ps.raw_off; g_par.size = ps.size;
-  g_par.tail = (uint32_t)ps.tail[0] | ((uint32_t)ps.tail[1] << 8) | ((uint32_t)ps.tail[2] << 16) | ((uint32_t)ps.tail[3] << 24);
   g_par.bins = bins_pool + ps.bin_off; g_par.bin_cap = ps.bin_cap; g_par.file_bin_base = ps.file_bin_base;
   g_par.blocks = blk_pool + ps.blk_off; g_par.nblk = 0; g_par.blk_cap = ps.blk_cap;
   g_par.emitted = 0; g_par.frame = ps.frame; g_par.mb_addr = 0; g_par.mb_w = ps.sp.mb_w;

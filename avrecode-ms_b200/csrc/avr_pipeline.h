@@ -163,7 +163,15 @@ static AVR_HDN void avr_pass_code(const uint16_t* prob, uint32_t e0, uint32_t e1
     const uint64_t w = nxt;
     p++; e += 4;
     if (e + 4 <= e1) nxt = p[0];
-    AVR_CODE_STEP(w & 0xFFFF); AVR_CODE_STEP((w >> 16) & 0xFFFF); AVR_CODE_STEP((w >> 32) & 0xFFFF); AVR_CODE_STEP(w >> 48);
+    // the divisor constants of all four records first: they depend on the records only, so their shared-memory
+    // latency overlaps the first symbol instead of opening every symbol's dependency chain
+    const uint32_t t0 = (uint32_t)(w >> 8) & 0x7F, t1 = (uint32_t)(w >> 24) & 0x7F, t2 = (uint32_t)(w >> 40) & 0x7F, t3 = (uint32_t)(w >> 56) & 0x7F;
+    const uint64_t m0 = dt->m[t0], m1 = dt->m[t1], m2 = dt->m[t2], m3 = dt->m[t3];
+    const uint32_t s0 = dt->s[t0], s1 = dt->s[t1], s2 = dt->s[t2], s3 = dt->s[t3];
+    enc.put((int)(w & 1), (AVR_MULHI64(enc.range, m0) >> s0) * (uint64_t)((w >> 1) & 0x7F));
+    enc.put((int)((w >> 16) & 1), (AVR_MULHI64(enc.range, m1) >> s1) * (uint64_t)((w >> 17) & 0x7F));
+    enc.put((int)((w >> 32) & 1), (AVR_MULHI64(enc.range, m2) >> s2) * (uint64_t)((w >> 33) & 0x7F));
+    enc.put((int)((w >> 48) & 1), (AVR_MULHI64(enc.range, m3) >> s3) * (uint64_t)((w >> 49) & 0x7F));
   }
   while (e < e1) { AVR_CODE_STEP(prob[e]); e++; }
 #undef AVR_CODE_STEP
