@@ -157,6 +157,8 @@ def main():
     import torch
     import avr_ctypes as A
     if world > 1:
+        # NCCL prints its version banner on stdout when NCCL_DEBUG is set: keep stdout for the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
