@@ -271,6 +271,13 @@ def main():
     except OSError:
         pass
     peak = peaks.get("hbm_gbs", 6650.0)
+    traffic = None
+    try:   # per-launch DRAM bytes of the dominant kernel from the committed ncu pass, valid for the default corpus only
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tr.get("clips") == args.clips:
+            traffic = tr["avr_k_decompress_chain"]["dram_read"] + tr["avr_k_decompress_chain"]["dram_write"]
+    except (OSError, KeyError, ValueError):
+        pass
     # dominant kernel: the decompress chain kernel (algorithmic bytes: payload read + CABAC bytes written)
     chain_s = chain_us / 1e6 / args.steps
     alg_bytes = payload_bytes + cabac_bytes
@@ -289,7 +296,7 @@ def main():
         "gpu_launches": int(launches_all),
         "clocks": clocks,
         "roofline": {"kernel": "avr_k_decompress_chain", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": traffic,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)",
                      "int_issue_frac": {"decompress": 56 * bins / chain_s / int_peak,
                                         "compress_coder": 32 * bins / (coder_us / 1e6 / args.steps) / int_peak,
