@@ -484,12 +484,22 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
     return fail(rc);
   avr_trace("dc: alloc");
   d.fds = d_fds; d.slices = d_ds; d.payloads = d_pay;
+  uint32_t* d_forder; if ((rc = m.alloc(&d_forder, (size_t)nfiles))) return fail(rc);
+  d.file_order = d_forder;
+  std::vector<uint32_t> forder((size_t)nfiles);
+  {
+    std::vector<uint64_t> fbytes((size_t)nfiles, 0);
+    for (int f = 0; f < nfiles; f++) for (uint32_t k = 0; k < fds[f].nslices; k++) fbytes[f] += ds[fds[f].slice_off + k].payload_len;
+    for (int f = 0; f < nfiles; f++) forder[f] = (uint32_t)f;
+    std::stable_sort(forder.begin(), forder.end(), [&](uint32_t a, uint32_t b) { return fbytes[a] > fbytes[b]; });
+  }
   cudaStream_t st = ctx->stream;
   cudaEventRecord(ctx->ev[0], st);
   uint64_t h2d = 0;
   auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };
   up(d_fds, fds.data(), fds.size() * sizeof(AvrFileDesc));
   up(d_ds, ds.data(), ds.size() * sizeof(AvrDecSlice));
+  up(d_forder, forder.data(), forder.size() * sizeof(uint32_t));
   {
     // one page-locked staging buffer and one copy instead of a pageable copy per slice
     size_t cap = 0;

@@ -258,33 +258,6 @@ AVR_DEC_INL int avr_dec_global(uint64_t& low, uint64_t& range, uint16_t* est, ui
   return symbol;
 }
 
-// ---- bin entry points outside residual blocks (one copy each in the kernel) --------------------
-AVR_DEC_FN int avr_dec_get(int ctx) {
-  uint64_t low = g_dec.low, range = g_dec.range;
-  const int sym = avr_dec_default(low, range, (uint32_t)ctx);
-  g_dec.low = low; g_dec.range = range;
-  g_dec.bins++;
-  avr_ring_post((uint32_t)ctx, sym);
-  return sym;
-}
-AVR_DEC_FN int avr_dec_bypass() {
-  uint64_t low = g_dec.low, range = g_dec.range;
-  const int sym = avr_dec_default(low, range, AVR_CTX_BYPASS);
-  g_dec.low = low; g_dec.range = range;
-  g_dec.bins++;
-  avr_ring_post(AVR_CTX_BYPASS, sym);
-  return sym;
-}
-AVR_DEC_FN int avr_dec_terminate() {
-  uint64_t low = g_dec.low, range = g_dec.range;
-  const int sym = avr_dec_default(low, range, AVR_CTX_TERMINATE);
-  g_dec.low = low; g_dec.range = range;
-  g_dec.bins++;
-  avr_ring_post(AVR_CTX_TERMINATE, sym);
-  if (sym) g_dec.done = 1;
-  return sym;
-}
-
 // address-space explicit accessors: avr_mem.h
 AVR_DEC_INL void avr_s_ld_ms(avr_sptr a, uint64_t& m, uint32_t& sh) { uint64_t t; avr_s_ld_2x64_ro(a, m, t); sh = (uint32_t)t; }
 AVR_DEC_INL void avr_ms_fill() {     // chain thread, once per file
@@ -361,6 +334,32 @@ AVR_DEC_INL void avr_cell_update2(uint32_t cell, uint32_t limit, uint32_t& u0, u
 AVR_DEC_INL avr_sptr avr_sbase() { return (avr_sptr)g_dec.self; }
 #define AVR_S_OFF(member) ((avr_sptr)offsetof(AvrDecShared, member))
 
+// ---- bin entry points outside residual blocks (one copy each in the kernel) --------------------
+AVR_DEC_INL int avr_dec_single(uint32_t key) {
+  const avr_sptr s_base = avr_sbase();
+  const avr_sptr s_ms = s_base + AVR_S_OFF(ms), s_ring = s_base + AVR_S_OFF(ring), a = s_base + AVR_S_OFF(est_def) + 2u * key;
+  uint64_t low = g_dec.low, range = g_dec.range;
+  uint32_t head = g_dec.ring_head, tail_seen = g_dec.ring_tail_seen;
+  AvrEstReg e; e.cell = avr_s_ld16(a); avr_est_consts(s_ms, e);
+  uint32_t u0, u1; avr_cell_update2(e.cell, 0x60, u0, u1);
+  const int sym = avr_dec_core(low, range, e);
+  avr_s_st16(a, sym ? u1 : u0);
+  avr_ring_reserve(head, tail_seen, 1);
+  avr_ring_store(s_ring, head, (key << 1) | (uint32_t)sym);
+  AVR_DEC_RENORM(low, range);
+  g_dec.low = low; g_dec.range = range;
+  g_dec.ring_head = head + 1; g_dec.ring_tail_seen = tail_seen;
+  g_dec.bins++;
+  return sym;
+}
+AVR_DEC_FN int avr_dec_get(int ctx) { return avr_dec_single((uint32_t)ctx); }
+AVR_DEC_FN int avr_dec_bypass() { return avr_dec_single(AVR_CTX_BYPASS); }
+AVR_DEC_FN int avr_dec_terminate() {
+  const int sym = avr_dec_single(AVR_CTX_TERMINATE);
+  if (sym) g_dec.done = 1;
+  return sym;
+}
+
 template <bool IS64>
 AVR_DEC_INL int avr_dec_sigmap(uint64_t& low, uint64_t& range, uint32_t& head, uint16_t* est, avr_sptr s_ms, avr_sptr s_ring,
                                uint32_t key0, int stored, int max_coeff, int sig_base, int last_base, int* last_out) {
@@ -419,7 +418,24 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
   avr_nz_ctx(&nc, g_dec.store[g_dec.cur], g_dec.store[g_dec.cur ^ 1], g_dec.mb_addr, g_dec.mb_w, n, max_coeff, cat, is_dc, 0);
   const int nbits = avr_nz_bits(max_coeff);
   int stored = 0;
-  for (int k = 0; k < nbits; k++) stored |= avr_dec_global(low, range, est, avr_nz_bit_key(nc, k, stored), 0x60) << k;
+  {
+    // the keys of bit i+1 for both values of bit i are known before bit i is decoded: their cells (sparse in the
+    // 2.7 MB pool, L2 more often than L1) and divisor constants are requested ahead
+    uint32_t k = avr_nz_bit_key(nc, 0, 0);
+    AvrEstReg e; e.cell = avr_g_ld16(est + k); avr_est_consts(s_ms, e);
+    for (int i = 0; i < nbits; i++) {
+      const int ni = i + 1 < nbits ? i + 1 : i;                  // past the last bit: any valid key
+      const uint32_t ka = avr_nz_bit_key(nc, ni, stored), kb = avr_nz_bit_key(nc, ni, stored | (1 << i));
+      AvrEstReg ea, eb; ea.cell = avr_g_ld16(est + ka); eb.cell = avr_g_ld16(est + kb);
+      avr_est_consts(s_ms, ea); avr_est_consts(s_ms, eb);
+      uint32_t u0, u1; avr_cell_update2(e.cell, 0x60, u0, u1);
+      const int bit = avr_dec_core(low, range, e);
+      avr_g_st16(est + k, bit ? u1 : u0);
+      AVR_DEC_RENORM(low, range);
+      stored |= bit << i;
+      e = bit ? eb : ea; k = bit ? kb : ka;
+    }
+  }
   if (stored == 0 && max_coeff <= 16) stored = max_coeff;
   // significance map
   const uint32_t key0 = avr_key_sig(cat, stored, 0, 0);

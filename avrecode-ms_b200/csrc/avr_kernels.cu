@@ -34,10 +34,13 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
 __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     const AvrFileDesc* fds, int nfiles, const AvrDecSlice* slices, const uint8_t* payloads, uint16_t* est_pool,
     uint8_t* store_pool, avr::MbInfo* row_pool, const AvrTables* tab, uint8_t* out, uint32_t* out_len, uint32_t* out_bins,
-    int* status) {
+    int* status, const uint32_t* file_order) {
   __shared__ int s_failed;
-  const int f = blockIdx.x, tid = threadIdx.x;
-  if (f >= nfiles) return;
+  const int tid = threadIdx.x;
+  if ((int)blockIdx.x >= nfiles) return;
+  // longest file first: consecutive blocks land on different SMs, so the long chains are spread instead of sharing
+  // issue slots with each other (the run lasts as long as the slowest chain)
+  const int f = file_order ? (int)file_order[blockIdx.x] : (int)blockIdx.x;
   const AvrFileDesc fd = fds[f];
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(&tab->hot);
@@ -158,7 +161,7 @@ int avr_launch_compress_chain(const AvrDevBatch& b, cudaStream_t st) {
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
   if (b.nfiles == 0) return 0;
   avr_k_decompress_chain<<<b.nfiles, AVR_DEC_THREADS, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
-                                                 b.tab, b.out, b.out_len, b.out_bins, b.status);
+                                                 b.tab, b.out, b.out_len, b.out_bins, b.status, b.file_order);
   return (int)cudaGetLastError();
 }
 

@@ -42,6 +42,7 @@ struct AvrDevDBatch {
   uint32_t nslices;
   const AvrFileDesc* fds;
   const AvrDecSlice* slices;
+  const uint32_t* file_order;      // files by descending payload bytes (block -> file), or null
   const uint8_t* payloads;
   const AvrTables* tab;
   uint16_t* est_pool;
