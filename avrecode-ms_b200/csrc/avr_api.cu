@@ -641,7 +641,10 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
     if (!sc.rc && sc.rec.out_of_domain) sc.rc = AVR_E_UNSUPPORTED;
   });
   avr_trace("cf: host scan");
-  // layout of the pools
+  // layout of the pools.  AVR_TEST_PARSE_CAP (tests only) lowers the record capacity so that the overflow -> host
+  // recorder fallback can be exercised with ordinary clips.
+  uint32_t bins_per_byte = 24u;
+  if (const char* e = getenv("AVR_TEST_PARSE_CAP")) { const int v = atoi(e); if (v >= 1 && v <= 24) bins_per_byte = (uint32_t)v; }
   std::vector<AvrParseSlice> ps; std::vector<uint64_t> row_off; std::vector<int> ps_file;
   std::vector<uint64_t> raw_base((size_t)nfiles, 0);
   uint64_t raw_bytes = 0, bin_pool = 0, blk_pool = 0, rows = 0;
@@ -654,7 +657,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
       p.raw_off = raw_base[f] + c.raw_off; p.size = c.size; memcpy(p.tail, c.tail, 4);
       // records per CABAC byte: ~11 bins typical; skip runs cost ~2 bins per macroblock and almost no bytes
       const uint32_t mbs = (uint32_t)c.sp.mb_w * (uint32_t)c.sp.mb_h;
-      p.bin_cap = 24u * c.size + 4u * (mbs > (uint32_t)c.sp.first_mb ? mbs - (uint32_t)c.sp.first_mb : 0u) + 2048u; p.blk_cap = p.bin_cap / 6;
+      p.bin_cap = bins_per_byte * c.size + 4u * (mbs > (uint32_t)c.sp.first_mb ? mbs - (uint32_t)c.sp.first_mb : 0u) + 2048u; p.blk_cap = p.bin_cap / 6;
       p.bin_off = bin_pool; bin_pool += p.bin_cap; p.blk_off = blk_pool; blk_pool += p.blk_cap;
       p.frame = c.frame; p.sp = c.sp;
       ps.push_back(p); ps_file.push_back(f); row_off.push_back(rows); rows += (uint64_t)c.sp.mb_w;

@@ -1,5 +1,6 @@
 // `recode` CLI, drop-in for the reference's (recode.cpp:1642-1677):
 //   recode compress|decompress|roundtrip <input> [output]      exit 0 / 1
+//   recode test <directory>                                     roundtrip of every regular file, <dir>/output/metrics.csv
 // plus the batch form the GPU path exists for:
 //   recode compress-batch|roundtrip-batch <file>...            outputs <file>.avrec / report only
 // All entropy coding runs on the GPU through include/avrecode_b200.h; there is no CPU path.
@@ -7,6 +8,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
+#include <filesystem>
 #include <string>
 #include <thread>
 #include <vector>
@@ -36,14 +39,73 @@ static double now_ms() {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// `recode test <dir>` (test.cpp:20-148): roundtrip of every regular file of the directory, decompressed copies in
+// <dir>/output/, results in <dir>/output/metrics.csv with the reference's columns (test.cpp:32) plus Bins and
+// Gbins/s.  The files go through the GPU as ONE batch, so the per-file times are the batch times apportioned by file
+// size; Duration / Video stream / Frames per second come from libavformat's dump in the reference and are "n/a" here.
+static int run_test(const std::string& dir, int threads) {
+  namespace fs = std::filesystem;
+  std::vector<std::string> names;
+  std::error_code ec;
+  for (const auto& e : fs::directory_iterator(dir, ec)) if (e.is_regular_file()) names.push_back(e.path().string());
+  if (ec) return fail("Failed to open directory: " + dir);
+  std::sort(names.begin(), names.end());
+  fs::create_directory(dir + "/output", ec);
+  const int n = (int)names.size();
+  std::vector<std::vector<uint8_t>> data((size_t)n);
+  for (int i = 0; i < n; i++) if (!read_file(names[i], &data[i])) return fail("Failed to open file: " + names[i]);
+  avr_context* ctx = nullptr;
+  if (avr_context_create(0, &ctx) != AVR_OK) return fail(avr_last_error());
+  std::vector<const uint8_t*> in, cin; std::vector<size_t> len, clen;
+  for (auto& d : data) { in.push_back(d.data()); len.push_back(d.size()); }
+  std::vector<avr_buffer> comp((size_t)n), dec((size_t)n);
+  avr_timing tc, td;
+  const double t0 = now_ms();
+  if (avr_compress_files(ctx, in.data(), len.data(), n, threads, comp.data(), &tc) != AVR_OK) return fail(avr_last_error());
+  const double t1 = now_ms();
+  for (auto& c : comp) { cin.push_back(c.data); clen.push_back(c.size); }
+  if (avr_decompress_files(ctx, cin.data(), clen.data(), n, threads, dec.data(), &td) != AVR_OK) return fail(avr_last_error());
+  const double t2 = now_ms();
+  double total = 0;
+  for (auto& d : data) total += (double)d.size();
+  FILE* csv = fopen((dir + "/output/metrics.csv").c_str(), "w");
+  if (!csv) return fail("Failed to open file: " + dir + "/output/metrics.csv");
+  fprintf(csv, "File,Duration,Initial size (MB),Compressed size (MB),Compression rate (%%),Space saving (%%),Total time (ms),Compression time (ms),"
+               "Compression speed (MB/s),Decompression time (ms),Decompression speed (MB/s),Video stream,Frames per second\n");
+  int failed = 0;
+  for (int i = 0; i < n; i++) {
+    const bool same = dec[i].size == data[i].size() && !memcmp(dec[i].data, data[i].data(), data[i].size());
+    if (!same) { failed++; continue; }                       // the reference leaves failed files out of the table (test.cpp:36-39)
+    const std::string base = names[i].substr(names[i].find_last_of('/') + 1);
+    write_out((dir + "/output/" + base).c_str(), dec[i].data, dec[i].size);
+    const double mb = data[i].size() / 1e6, share = total > 0 ? data[i].size() / total : 0.0;
+    const double cms = (t1 - t0) * share, dms = (t2 - t1) * share, rate = data[i].empty() ? 0.0 : 100.0 * comp[i].size / data[i].size();
+    fprintf(csv, "\"%s\",n/a,%g,%g,%g,%g,%g,%g,%g,%g,%g,n/a,n/a\n", names[i].c_str(), mb, mb * rate / 100.0, rate, 100.0 - rate, cms + dms, cms,
+            cms > 0 ? mb / (cms / 1e3) : 0.0, dms, dms > 0 ? mb / (dms / 1e3) : 0.0);
+  }
+  fclose(csv);
+  FILE* log = fopen((dir + "/output/log.txt").c_str(), "w");
+  if (log) {
+    fprintf(log, "files %d  bytes %.0f  bins %llu\ncompress %.1f ms (parse %.1f, kernels %.1f)  decompress %.1f ms (kernel %.1f)\n", n, total,
+            (unsigned long long)tc.bins, t1 - t0, tc.parse_ms, tc.kernel_ms, t2 - t1, td.kernel_ms);
+    fclose(log);
+  }
+  printf("%d files, %.1f MB: compress %.1f MB/s, decompress %.1f MB/s, %.2f Gbins/s roundtrip\n", n, total / 1e6, total / 1e3 / (t1 - t0),
+         total / 1e3 / (t2 - t1), tc.bins / 1e6 / (t2 - t0));
+  if (failed) printf("Compress-decompress roundtrip failed on %d / %d files\n", failed, n);
+  avr_context_destroy(ctx);
+  return failed ? 1 : 0;
+}
+
 int main(int argc, char** argv) {
   if (argc < 3) {
-    fprintf(stderr, "Usage: %s [compress|decompress|roundtrip] <input> [output]\n", argv[0]);
+    fprintf(stderr, "Usage: %s [compress|decompress|roundtrip|test] <input> [output]\n", argv[0]);
     return 1;
   }
   std::string cmd = argv[1];
   int threads = (int)std::thread::hardware_concurrency();
   if (threads < 1) threads = 1;
+  if (cmd == "test") return run_test(argv[2], threads);
   bool batch = cmd == "compress-batch" || cmd == "roundtrip-batch";
   if (!batch && cmd != "compress" && cmd != "decompress" && cmd != "roundtrip") {
     fprintf(stderr, "Unknown command: %s\n", cmd.c_str());

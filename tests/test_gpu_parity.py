@@ -5,7 +5,7 @@ import os
 import pytest
 
 from avrec_wire import parse_avrec
-from conftest import GOLDEN, GOLDEN_NAMES, REF, gen_clip, have_ref, oracle_encode, ref_trace, run, golden_trace
+from conftest import GOLDEN, GOLDEN_NAMES, REF, ROOT, gen_clip, have_ref, oracle_encode, ref_trace, run, golden_trace
 
 pytestmark = pytest.mark.gpu
 
@@ -73,6 +73,54 @@ def test_host_parse_path_gives_the_same_containers(ctx, tmpdir_path, monkeypatch
     assert dev == host
     assert td["parse_ms"] > 0 and th["parse_ms"] == 0
     assert td["coded_symbols"] == th["coded_symbols"]
+
+
+def test_device_parse_overflow_falls_back_to_host_recorder(ctx, monkeypatch):
+    """record capacity exceeded on the device -> that file goes through the host recorder; same container"""
+    import avr_ctypes as A
+    datas = [open(os.path.join(GOLDEN, n + ".h264"), "rb").read() for n in GOLDEN_NAMES]
+    monkeypatch.setenv("AVR_TEST_PARSE_CAP", "1")
+    b = A.CBatch(ctx, files=datas)
+    assert any(st == -3 for st in b.file_status), b.file_status      # AVR_E_OVERFLOW
+    b.close()
+    comp, t = A.compress_files(ctx, datas)
+    monkeypatch.delenv("AVR_TEST_PARSE_CAP")
+    for n, c in zip(GOLDEN_NAMES, comp):
+        assert c == open(os.path.join(GOLDEN, n + ".avrec"), "rb").read(), n
+
+
+def test_cli_recode_test_directory(ctx, tmpdir_path):
+    """`recode test <dir>` (test.cpp): decompressed copies + metrics.csv with the reference's columns"""
+    import shutil
+    d = os.path.join(tmpdir_path, "corpus")
+    os.makedirs(d)
+    for n in GOLDEN_NAMES[:3]:
+        shutil.copy(os.path.join(GOLDEN, n + ".h264"), d)
+    rc, out, err = run([os.path.join(ROOT, "avrecode-ms_b200", "bin", "recode"), "test", d])
+    assert rc == 0, out + err
+    rows = open(os.path.join(d, "output", "metrics.csv")).read().splitlines()
+    assert rows[0].startswith("File,Duration,Initial size (MB),Compressed size (MB),Compression rate (%),Space saving (%),Total time (ms)")
+    assert len(rows) == 4
+    for n in GOLDEN_NAMES[:3]:
+        assert open(os.path.join(d, "output", n + ".h264"), "rb").read() == open(os.path.join(GOLDEN, n + ".h264"), "rb").read()
+
+
+def test_cli_matches_reference_cli_shape(ctx, tmpdir_path):
+    """compress / decompress / roundtrip: same arguments, container bytes and exit codes as the reference's CLI"""
+    exe = os.path.join(ROOT, "avrecode-ms_b200", "bin", "recode")
+    src = os.path.join(GOLDEN, "multislice.h264") if os.path.exists(os.path.join(GOLDEN, "multislice.h264")) else os.path.join(GOLDEN, GOLDEN_NAMES[0] + ".h264")
+    name = os.path.basename(src)[:-5]
+    avrec, back = os.path.join(tmpdir_path, "x.avrec"), os.path.join(tmpdir_path, "x.h264")
+    assert run([exe, "compress", src, avrec])[0] == 0
+    assert open(avrec, "rb").read() == open(os.path.join(GOLDEN, name + ".avrec"), "rb").read()
+    assert run([exe, "decompress", avrec, back])[0] == 0
+    assert open(back, "rb").read() == open(src, "rb").read()
+    rc, out, _ = run([exe, "compress", src])                       # stdout when no output is named (recode.cpp:1659)
+    assert rc == 0 and out == open(avrec, "rb").read()
+    assert run([exe, "roundtrip", src])[0] == 0
+    assert run([exe, "decompress", src, back])[0] == 1             # not a container -> exit 1
+    assert run([exe, "frobnicate", src])[0] == 1
+    assert run([exe, "compress", os.path.join(tmpdir_path, "missing.h264")])[0] == 1
 
 
 def test_decompress_reference_containers(ctx):
