@@ -201,3 +201,25 @@ def test_large_roundtrip_property(ctx, tmpdir_path):
     for mode in (0, 1):
         b = A.CBatch(ctx, [rec]); b.run(mode); b.fetch(); res.append(b.payloads()); b.close()
     assert res[0] == res[1]
+
+
+@pytest.mark.parametrize("shape", [
+    dict(seed=61, mb_w=240, mb_h=135, frames=2, slices_per_frame=68, p_sig=150, p_cbf=230, p_cbp=240, transform_8x8=1),   # config 5: 2160p, 68 slices/frame, dense residuals
+    dict(seed=62, mb_w=120, mb_h=68, frames=12, slices_per_frame=8, num_ref=3),                                          # config 3: 1080p, 8 slices/frame
+])
+def test_baseline_config_shapes_roundtrip(ctx, tmpdir_path, shape):
+    """BASELINE configs[2] / configs[4] picture and slice geometry (fewer frames): roundtrip == input, device parse ==
+    host parse, pipeline == chain"""
+    import avr_ctypes as A
+    data = gen_clip(os.path.join(tmpdir_path, "cfg.h264"), **shape)
+    comp, tc = A.compress_files(ctx, [data])
+    back, td = A.decompress_files(ctx, comp)
+    assert back[0] == data
+    assert tc["parse_ms"] > 0 and tc["bins"] == td["bins"] > 1_000_000
+    rec = A.Record(data)
+    assert rec.rc == 0 and rec.slices >= shape["frames"] * (shape["slices_per_frame"] - 1)
+    b = A.CBatch(ctx, [rec]); b.run(A.MODE_CHAIN); b.fetch()
+    want = b.payloads()[0]
+    b.close(); rec.close()
+    got = [blk["cabac"] for blk in parse_avrec(comp[0]) if "cabac" in blk]
+    assert got == want
