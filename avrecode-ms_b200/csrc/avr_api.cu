@@ -601,6 +601,7 @@ extern "C" void avr_dbatch_destroy(avr_dbatch* b) {
 
 // ---- compress batch from raw files: device-side parse (avr_parse.h) ---------------------------
 #include <atomic>
+#include <mutex>
 #include <chrono>
 #include <thread>
 #include "avr_parse.h"
@@ -625,6 +626,7 @@ struct AvrFileScan {
 // kept by the batch for container building
 struct avr_cbatch_files { std::vector<AvrFileScan> scans; };
 static std::vector<std::pair<avr_cbatch*, avr_cbatch_files*>>& files_registry() { static std::vector<std::pair<avr_cbatch*, avr_cbatch_files*>> r; return r; }
+static std::mutex& files_registry_mu() { static std::mutex m; return m; }   // contexts of different GPUs may live on different threads
 
 extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* files, const size_t* lens, int nfiles,
                                        int host_threads, avr_cbatch** out, int* file_status) {
@@ -774,12 +776,13 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   tmp.release();
   b->t.host_ms = wall_ms() - t_host0 - b->t.h2d_ms - b->t.parse_ms;
   avr_trace("cf: free tmp");
-  files_registry().push_back({b, bf});
+  { std::lock_guard<std::mutex> g(files_registry_mu()); files_registry().push_back({b, bf}); }
   *out = b;
   return AVR_OK;
 }
 
 static avr_cbatch_files* files_of(const avr_cbatch* b) {
+  std::lock_guard<std::mutex> g(files_registry_mu());
   for (auto& p : files_registry()) if (p.first == b) return p.second;
   return nullptr;
 }
@@ -799,6 +802,7 @@ extern "C" int avr_cbatch_span(const avr_cbatch* b, int file, uint32_t i, uint64
   return AVR_OK;
 }
 void avr_cbatch_files_release(avr_cbatch* b) {
+  std::lock_guard<std::mutex> g(files_registry_mu());
   auto& r = files_registry();
   for (size_t i = 0; i < r.size(); i++) if (r[i].first == b) { delete r[i].second; r.erase(r.begin() + i); return; }
 }

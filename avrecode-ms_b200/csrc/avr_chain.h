@@ -63,9 +63,8 @@ static AVR_HD uint32_t avr_nz_bit_key(const AvrNzCtx& c, int i, int so_far) {
 }
 // cur / prev = base of the 64-byte-per-MB stores of the current and previous picture (prev may
 // be null = all zero).  Only valid after the block's own is_8x8 contribution has been stored.
-static AVR_HD void avr_nz_ctx(AvrNzCtx* c, const uint8_t* cur, const uint8_t* prev, uint32_t mb_addr, int mb_w,
-                              int n, int size, int cat, int is_dc, int c422) {
-  int mb_x = (int)(mb_addr % (uint32_t)mb_w);
+static AVR_HD void avr_nz_ctx_x(AvrNzCtx* c, const uint8_t* cur, const uint8_t* prev, uint32_t mb_addr, int mb_x, int mb_w,
+                                int n, int size, int cat, int is_dc, int c422) {
   int cross, nn;
   nn = avr_neighbor_n(n, 0, size, &cross);
   c->has_left = !(cross && mb_x == 0);
@@ -76,6 +75,11 @@ static AVR_HD void avr_nz_ctx(AvrNzCtx* c, const uint8_t* cur, const uint8_t* pr
   c->prev_nz = prev ? prev[(size_t)mb_addr * AVR_MB_STRIDE + n] : 0;
   int is8 = cur[(size_t)mb_addr * AVR_MB_STRIDE + AVR_MB_IS8X8] || size > 32;
   c->third = is8 + 2 * is_dc + c422 + 4 * cat;
+}
+
+static AVR_HD void avr_nz_ctx(AvrNzCtx* c, const uint8_t* cur, const uint8_t* prev, uint32_t mb_addr, int mb_w,
+                              int n, int size, int cat, int is_dc, int c422) {
+  avr_nz_ctx_x(c, cur, prev, mb_addr, (int)(mb_addr % (uint32_t)mb_w), mb_w, n, size, cat, is_dc, c422);
 }
 
 struct AvrChain {

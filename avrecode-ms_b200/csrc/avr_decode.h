@@ -52,7 +52,7 @@ struct AvrDecShared {
   uint16_t* est;                               // global: sig-map and nnz-bit estimators
   uint8_t* store[2];
   int cur, mb_w;
-  uint32_t mb_addr;
+  uint32_t mb_addr, mb_x;
   uint32_t bins;
   int done;
   uint64_t self;                               // shared-window address of this object, read back as an opaque value (see avr_sbase)
@@ -415,7 +415,7 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
   // nnz bits first.  The count is recovered completely (a block that codes as 0 in 2/4 bits is a
   // full one) so that the store holds what the COMPRESSOR held.
   AvrNzCtx nc;
-  avr_nz_ctx(&nc, g_dec.store[g_dec.cur], g_dec.store[g_dec.cur ^ 1], g_dec.mb_addr, g_dec.mb_w, n, max_coeff, cat, is_dc, 0);
+  avr_nz_ctx_x(&nc, g_dec.store[g_dec.cur], g_dec.store[g_dec.cur ^ 1], g_dec.mb_addr, (int)g_dec.mb_x, g_dec.mb_w, n, max_coeff, cat, is_dc, 0);
   const int nbits = avr_nz_bits(max_coeff);
   int stored = 0;
   {
@@ -465,13 +465,17 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
     const int i2 = node_ctx < 4 ? 5 : (node_ctx + 2 > gt1_max ? gt1_max : node_ctx + 2);
     const avr_sptr a2 = s_abs + 2u * (uint32_t)i2;
     AvrEstReg e2; e2.cell = avr_s_ld16(a2); avr_est_consts(s_ms, e2);   // used only if b0 = 1; its latency hides behind b0
+    // node_ctx after this coefficient and the address of the next b0 estimator, for both outcomes (selects, no branches)
+    const int nn0 = node_ctx < 3 ? node_ctx + 1 : node_ctx;
+    const int nn1 = node_ctx < 4 ? 4 : (node_ctx < 7 ? node_ctx + 1 : 7);
+    const avr_sptr a10 = s_abs + 2u * (uint32_t)(nn0 < 4 ? nn0 + 1 : 0), a11 = s_abs + 2u * (uint32_t)(nn1 < 4 ? nn1 + 1 : 0);
     uint32_t u0, u1; avr_cell_update2(e1.cell, 0x60, u0, u1);
     const int b0 = avr_dec_core(low, range, e1);
     avr_s_st16(a1, b0 ? u1 : u0);
     avr_ring_store(s_ring, head++, (rec_abs + 2u * (uint32_t)i1) | (uint32_t)b0);
     // node_ctx and ctx1 of the next coefficient are known now: request that cell behind the store above
-    node_ctx = b0 ? (node_ctx < 4 ? 4 : (node_ctx < 7 ? node_ctx + 1 : 7)) : (node_ctx < 3 ? node_ctx + 1 : node_ctx);
-    a1 = s_abs + 2u * (uint32_t)(node_ctx < 4 ? node_ctx + 1 : 0);
+    node_ctx = b0 ? nn1 : nn0;
+    a1 = b0 ? a11 : a10;
     e1.cell = avr_s_ld16(a1); avr_est_consts(s_ms, e1);
     AVR_DEC_RENORM(low, range);
     if (b0) {
@@ -519,7 +523,7 @@ struct AvrDecPolicy {
   AVR_DEC_M int get(int ctx) { return avr_dec_get(ctx); }
   AVR_DEC_M int bypass(int) { return avr_dec_bypass(); }
   AVR_DEC_M int terminate(int) { return avr_dec_terminate(); }
-  AVR_DEC_M void mb_begin(int x, int y) { g_dec.mb_addr = (uint32_t)(x + y * g_dec.mb_w); }
+  AVR_DEC_M void mb_begin(int x, int y) { g_dec.mb_addr = (uint32_t)(x + y * g_dec.mb_w); g_dec.mb_x = (uint32_t)x; }
   AVR_DEC_M void sub_mb_begin(int, int, int, int, int) {}
   AVR_DEC_M void sub_mb_end() {}
   AVR_DEC_M void sigmap_begin() {}
