@@ -303,6 +303,14 @@ def main():
                                         "note": "planning ops/bin (SURVEY 8d) / (148 SM x 128 lanes x SM clock)"}},
         "single_clip": single,
     }
+    if single:
+        # what actually bounds the dominant kernel: the dependent-issue latency of ONE thread per file
+        line["roofline"]["serial_chain"] = {
+            "mbins_s_per_chain": single["decompress_mbins_s"],
+            "cycles_per_bin": sm_mhz / single["decompress_mbins_s"],
+            "recurrence_floor_cycles": 60,
+            "note": "low/range -> symbol -> low/range recurrence (64x64 mul-high, shift, mul, sub, compare, select) ~60 cycles; "
+                    "the run lasts as long as the longest chain of the batch"}
     if world == 1:
         # CPU baseline beside it (rank 0, N=1 only): bounded sample of the same corpus
         if os.path.exists(os.path.join(REF, "recode")):
