@@ -142,7 +142,8 @@ static int compress_pipeline(const std::vector<const avr::FileRecord*>& recs, co
   return 0;
 }
 
-static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRecord& rec, const AvrTables& tab, const Compressed& c) {
+static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRecord& rec, const AvrTables& tab, const Compressed& c,
+                            uint32_t fuzz_seed = 0, int fuzz_flips = 0) {
   AvrFileDesc fd = make_desc(rec);
   std::vector<AvrDecSlice> ds;
   std::vector<uint8_t> pool;
@@ -173,8 +174,20 @@ static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRec
   std::vector<uint32_t> olen(ds.size()), obins(ds.size());
   std::vector<int> status(ds.size());
   pool.resize(pool.size() + 16);
+  if (fuzz_flips) {   // corrupt the payload pool: the chain must end every slice with a status, inside its buffers
+    uint32_t x = fuzz_seed * 2654435761u + 12345u;
+    for (int k = 0; k < fuzz_flips && pool.size() > 16; k++) {
+      x = x * 1664525u + 1013904223u; const size_t pos = (x >> 8) % (pool.size() - 16);
+      x = x * 1664525u + 1013904223u; pool[pos] ^= (uint8_t)(1u << ((x >> 13) & 7));
+    }
+  }
   avr_decompress_file_host(fd, ds.data(), pool.data(), est.data(), s0.data(), s1.data(), row.data(), &tab,
                            out.data(), olen.data(), obins.data(), status.data());
+  if (fuzz_flips) {
+    int nerr = 0; for (int v : status) nerr += v != 0;
+    printf("TERMINATED slices=%zu with_status=%d\n", ds.size(), nerr);
+    return 0;
+  }
   int bad = 0;
   uint64_t bins = 0;
   for (size_t s = 0; s < ds.size(); s++) {
@@ -196,7 +209,7 @@ static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRec
 }
 
 // device-side parse body (avr_parse.h) on the host, slice by slice, against the host recorder
-static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& want, const AvrTables& tab) {
+static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& want, const AvrTables& tab, uint32_t fuzz_seed = 0, int fuzz_flips = 0) {
   avr::FileRecord scan;
   std::vector<avr::ScanSlice> coded;
   int rc = avr::scan_annexb(data.data(), data.size(), &scan, &coded);
@@ -204,7 +217,16 @@ static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& 
   std::vector<uint16_t> bins; std::vector<AvrBlock> blocks;
   avr_par_tables(&tab, 0, 1);
   std::vector<uint8_t> raw(data); raw.resize(raw.size() + 16);
+  if (fuzz_flips) {   // corrupt CABAC payload bytes only (headers were scanned from the intact file)
+    uint32_t x = fuzz_seed * 2654435761u + 777u;
+    for (int k = 0; k < fuzz_flips && !coded.empty(); k++) {
+      x = x * 1664525u + 1013904223u; const avr::ScanSlice& c = coded[(x >> 8) % coded.size()];
+      x = x * 1664525u + 1013904223u; const size_t pos = c.raw_off + (x >> 8) % c.size;
+      x = x * 1664525u + 1013904223u; raw[pos] ^= (uint8_t)(1u << ((x >> 13) & 7));
+    }
+  }
   uint64_t emitted = 0;
+  int with_status = 0;
   for (const avr::ScanSlice& c : coded) {
     AvrParseSlice ps;
     memset(&ps, 0, sizeof ps);
@@ -216,11 +238,13 @@ static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& 
     AvrParseResult res;
     avr_body_patch_tail(ps, raw.data());
     avr_parse_slice(ps, raw.data(), b.data(), k.data(), row.data(), &res);
+    if (fuzz_flips) { with_status += res.status != 0; continue; }
     if (res.status) { printf("slice status %d\n", res.status); return 1; }
     bins.insert(bins.end(), b.begin(), b.begin() + res.nbins);
     blocks.insert(blocks.end(), k.begin(), k.begin() + res.nblocks);
     emitted += res.emitted;
   }
+  if (fuzz_flips) { printf("TERMINATED slices=%zu with_status=%d\n", coded.size(), with_status); return 0; }
   bool ok = bins == want.bins && blocks.size() == want.blocks.size() && emitted == want.emitted &&
             scan.spans.size() == want.spans.size() && scan.frames.size() == want.frames.size();
   for (size_t i = 0; ok && i < blocks.size(); i++) ok = !memcmp(&blocks[i], &want.blocks[i], sizeof(AvrBlock));
@@ -239,6 +263,11 @@ int main(int argc, char** argv) {
   AvrTables tab;
   avr_fill_tables(&tab);
   Compressed c;
+  // fuzzdec / fuzzparse <clip> <seed> <flips>: corrupted inputs must terminate with statuses and stay inside their buffers
+  // (run under -fsanitize=address by tests/test_host_logic.py)
+  const uint32_t fseed = argc > 3 ? (uint32_t)atoi(argv[3]) : 1; const int fflips = argc > 4 ? atoi(argv[4]) : 8;
+  if (cmd == "fuzzparse") return parse_check(data, rec, tab, fseed, fflips);
+  if (cmd == "fuzzdec") { if (compress_chain(rec, tab, &c)) return 1; return decompress_check(data, rec, tab, c, fseed, fflips); }
   if (cmd == "chain" || cmd == "roundtrip") {
     if (compress_chain(rec, tab, &c)) return 1;
   }

@@ -9,6 +9,7 @@ from avrec_wire import parse_avrec
 from conftest import GOLDEN, GOLDEN_NAMES, ROOT, gen_clip, have_ref, hex_payloads, oracle_encode, ref_trace, run
 
 EMUL = os.path.join(ROOT, "build", "avr_emul")
+EMUL_ASAN = os.path.join(ROOT, "build", "avr_emul_asan")
 
 
 def golden_payloads(name):
@@ -64,3 +65,14 @@ def test_bodies_match_oracle_on_fresh_clips(params, tmpdir_path):
     for cmd in ("roundtrip", "parse"):
         rc, out, err = run([EMUL, cmd, clip])
         assert rc == 0 and out.startswith(b"OK"), out + err
+
+
+@pytest.mark.parametrize("cmd", ["fuzzdec", "fuzzparse"])
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_corrupted_input_ends_with_a_status_inside_its_buffers(name, cmd):
+    """bit flips in the range-coded payloads (decompress body) or in the CABAC slice bytes (parse body):
+    every slice must end -- with a status or a (wrong) result -- without reading or writing outside its
+    buffers.  Runs the device bodies under ASan + UBSan; any report fails the test."""
+    for seed, flips in ((1, 1), (2, 8), (3, 64), (4, 8)):
+        rc, out, err = run([EMUL_ASAN, cmd, os.path.join(GOLDEN, name + ".h264"), str(seed), str(flips)], timeout=120)
+        assert rc == 0 and b"TERMINATED" in out and b"runtime error" not in err and b"ERROR" not in err, out + err
