@@ -22,7 +22,10 @@ EXPORTS = [
     "avr_cbatch_create", "avr_cbatch_create_files", "avr_cbatch_span_count", "avr_cbatch_span", "avr_cbatch_run", "avr_cbatch_fetch", "avr_cbatch_payload", "avr_cbatch_timing",
     "avr_cbatch_destroy", "avr_dbatch_create", "avr_dbatch_run", "avr_dbatch_fetch", "avr_dbatch_slice",
     "avr_dbatch_timing", "avr_dbatch_destroy", "avr_compress_files", "avr_decompress_files", "avr_buffer_free",
+    "avr_streams_encode", "avr_streams_decode",
 ]
+STREAM_FIXED_HALF = 0
+STREAM_ADAPTIVE = 1
 
 
 class SliceParams(C.Structure):
@@ -97,6 +100,10 @@ def lib():
                                          C.POINTER(Buffer), C.POINTER(Timing)]
         L.avr_decompress_files.argtypes = L.avr_compress_files.argtypes
         L.avr_buffer_free.argtypes = [C.POINTER(Buffer)]
+        L.avr_streams_encode.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(Buffer),
+                                         C.POINTER(C.c_uint64), C.POINTER(Timing)]
+        L.avr_streams_decode.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64), C.c_uint32, C.c_uint32, C.c_int, C.c_int,
+                                         C.c_char_p, C.POINTER(Timing)]
         _lib = L
     return _lib
 
@@ -266,3 +273,26 @@ def compress_files(ctx, blobs, threads=0):
 def decompress_files(ctx, blobs, threads=0):
     """`recode decompress` for a batch of .avrec byte strings -> original byte strings."""
     return _files_call(lib().avr_decompress_files, ctx, blobs, threads or (os.cpu_count() or 1))
+
+
+def streams_encode(ctx, bits, nstreams, nbins, digit_bits=16, model=STREAM_FIXED_HALF):
+    """bits: bytes of nstreams * nbins 0/1 values (stream-major).  Returns ([coded bytes per stream], timing dict)."""
+    assert len(bits) == nstreams * nbins
+    buf, t = Buffer(), Timing()
+    off = (C.c_uint64 * (nstreams + 1))()
+    _check(lib().avr_streams_encode(ctx.h, bytes(bits), nstreams, nbins, digit_bits, model, C.byref(buf), off, C.byref(t)))
+    blob = C.string_at(buf.data, buf.size) if buf.size else b""
+    lib().avr_buffer_free(C.byref(buf))
+    return [blob[off[s]:off[s + 1]] for s in range(nstreams)], t.as_dict()
+
+
+def streams_decode(ctx, coded, nstreams, nbins, digit_bits=16, model=STREAM_FIXED_HALF):
+    """coded: list of per-stream bytes.  Returns (bytes of nstreams * nbins 0/1 values, timing dict)."""
+    assert len(coded) == nstreams
+    off = (C.c_uint64 * (nstreams + 1))()
+    for s, c in enumerate(coded):
+        off[s + 1] = off[s] + len(c)
+    out = C.create_string_buffer(max(nstreams * nbins, 1))
+    t = Timing()
+    _check(lib().avr_streams_decode(ctx.h, b"".join(coded), off, nstreams, nbins, digit_bits, model, out, C.byref(t)))
+    return out.raw[:nstreams * nbins], t.as_dict()

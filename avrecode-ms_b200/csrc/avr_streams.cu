@@ -1,0 +1,177 @@
+// avr_streams_encode / avr_streams_decode: S independent bin streams through the generic range coder on the GPU
+// (BASELINE configs[0]; bodies and reference citations in avr_streams.h).  One stream per thread, 128 streams per
+// block; per-stream scratch is compacted by the same device-side exclusive scan + gather the slice payloads use.
+#include <cuda_runtime.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
+#include "../../include/avrecode_b200.h"
+#include "avr_api_internal.h"
+#include "avr_kernels.h"
+#include "avr_streams.h"
+
+#define AVR_STREAM_BLOCK 128
+
+template <int DIGIT_BITS, int MODEL>
+__global__ void __launch_bounds__(AVR_STREAM_BLOCK) avr_k_stream_encode(const uint8_t* bits, uint32_t nstreams, uint32_t nbins,
+                                                                        const AvrDivTab* div, uint8_t* scratch, uint32_t cap,
+                                                                        uint32_t* len, int* status) {
+  __shared__ AvrDivTab dt;
+  if (MODEL == AVR_STREAM_ADAPTIVE) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(div);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&dt);
+    for (uint32_t i = threadIdx.x; i < sizeof(AvrDivTab) / 4; i += AVR_STREAM_BLOCK) dst[i] = src[i];
+    __syncthreads();
+  }
+  const uint32_t s = blockIdx.x * AVR_STREAM_BLOCK + threadIdx.x;
+  if (s < nstreams) avr_body_stream_encode<DIGIT_BITS, MODEL>(s, bits, nbins, &dt, scratch, cap, len, status);
+}
+
+template <int DIGIT_BITS, int MODEL>
+__global__ void __launch_bounds__(AVR_STREAM_BLOCK) avr_k_stream_decode(const uint8_t* coded, const uint64_t* coded_off, uint32_t nstreams,
+                                                                        uint32_t nbins, const AvrDivTab* div, uint8_t* bits_out) {
+  __shared__ AvrDivTab dt;
+  if (MODEL == AVR_STREAM_ADAPTIVE) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(div);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&dt);
+    for (uint32_t i = threadIdx.x; i < sizeof(AvrDivTab) / 4; i += AVR_STREAM_BLOCK) dst[i] = src[i];
+    __syncthreads();
+  }
+  const uint32_t s = blockIdx.x * AVR_STREAM_BLOCK + threadIdx.x;
+  if (s < nstreams) avr_body_stream_decode<DIGIT_BITS, MODEL>(s, coded, coded_off, nbins, &dt, bits_out);
+}
+
+#define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { avr_set_error("%s: %s", #x, cudaGetErrorString(e_)); rc = AVR_E_CUDA; goto done; } } while (0)
+
+static int check_args(avr_context* ctx, uint32_t nstreams, uint32_t nbins, int digit_bits, int model) {
+  if (!ctx) { avr_set_error("streams: no context (this library has no CPU path)"); return AVR_E_ARG; }
+  if (digit_bits != 8 && digit_bits != 16) { avr_set_error("streams: digit_bits must be 8 or 16"); return AVR_E_ARG; }
+  if (model != AVR_STREAM_FIXED_HALF && model != AVR_STREAM_ADAPTIVE) { avr_set_error("streams: unknown model %d", model); return AVR_E_ARG; }
+  if ((uint64_t)nbins + 64 > 0xFFFFFFFFull / 2) { avr_set_error("streams: nbins too large"); return AVR_E_ARG; }
+  (void)nstreams;
+  return AVR_OK;
+}
+static float ev_ms(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
+
+extern "C" int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_t nstreams, uint32_t nbins, int digit_bits, int model,
+                                  avr_buffer* coded, uint64_t* coded_off, avr_timing* t) {
+  int rc = check_args(ctx, nstreams, nbins, digit_bits, model);
+  if (rc) return rc;
+  if (!coded || !coded_off || (!bits && nstreams && nbins)) { avr_set_error("streams: null argument"); return AVR_E_ARG; }
+  coded->data = nullptr; coded->size = 0;
+  if (t) memset(t, 0, sizeof *t);
+  if (nstreams == 0) { coded_off[0] = 0; return AVR_OK; }
+  cudaStream_t st = (cudaStream_t)avr_context_stream(ctx);
+  const uint32_t cap = avr_stream_cap(nbins, model);
+  const size_t nbytes = (size_t)nstreams * nbins;
+  uint8_t *d_bits = nullptr, *d_scratch = nullptr, *d_out = nullptr;
+  uint32_t* d_len = nullptr; int* d_status = nullptr; uint64_t *d_off = nullptr; AvrDivTab* d_div = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::vector<int> status(nstreams);
+  std::vector<uint32_t> len(nstreams);
+  uint64_t total = 0;
+  const AvrDivTab h_div = AVR_DIV_TAB_INIT;
+  const uint32_t grid = (nstreams + AVR_STREAM_BLOCK - 1) / AVR_STREAM_BLOCK;
+  for (auto& e : ev) CU(cudaEventCreate(&e));
+  CU(cudaMalloc(&d_bits, nbytes + 8));
+  CU(cudaMalloc(&d_scratch, (size_t)nstreams * cap));
+  CU(cudaMalloc(&d_out, (size_t)nstreams * cap));
+  CU(cudaMalloc(&d_len, sizeof(uint32_t) * nstreams));
+  CU(cudaMalloc(&d_status, sizeof(int) * nstreams));
+  CU(cudaMalloc(&d_off, sizeof(uint64_t) * (nstreams + 1)));
+  CU(cudaMalloc(&d_div, sizeof(AvrDivTab)));
+  CU(cudaEventRecord(ev[0], st));
+  CU(cudaMemcpyAsync(d_div, &h_div, sizeof h_div, cudaMemcpyHostToDevice, st));
+  if (nbytes) CU(cudaMemcpyAsync(d_bits, bits, nbytes, cudaMemcpyHostToDevice, st));
+  CU(cudaEventRecord(ev[1], st));
+#define LAUNCH_ENC(D, M) avr_k_stream_encode<D, M><<<grid, AVR_STREAM_BLOCK, 0, st>>>(d_bits, nstreams, nbins, d_div, d_scratch, cap, d_len, d_status)
+  if (digit_bits == 8) { if (model == AVR_STREAM_ADAPTIVE) LAUNCH_ENC(8, AVR_STREAM_ADAPTIVE); else LAUNCH_ENC(8, AVR_STREAM_FIXED_HALF); }
+  else { if (model == AVR_STREAM_ADAPTIVE) LAUNCH_ENC(16, AVR_STREAM_ADAPTIVE); else LAUNCH_ENC(16, AVR_STREAM_FIXED_HALF); }
+#undef LAUNCH_ENC
+  CU(cudaGetLastError());
+  {
+    // per-stream scratch -> one contiguous buffer (device-side exclusive scan of the lengths, then a gather)
+    std::vector<uint64_t> soff(nstreams);
+    for (uint32_t s = 0; s < nstreams; s++) soff[s] = (uint64_t)s * cap;
+    uint64_t* d_soff = nullptr;
+    CU(cudaMalloc(&d_soff, sizeof(uint64_t) * nstreams));
+    cudaError_t e1 = cudaMemcpyAsync(d_soff, soff.data(), sizeof(uint64_t) * nstreams, cudaMemcpyHostToDevice, st);
+    int lrc = e1 == cudaSuccess ? avr_launch_compact(d_scratch, d_soff, d_len, d_off, d_off + nstreams, d_out, nstreams, st) : (int)e1;
+    cudaError_t e2 = cudaEventRecord(ev[2], st);
+    cudaError_t e3 = cudaStreamSynchronize(st);
+    cudaFree(d_soff);
+    if (lrc || e2 != cudaSuccess || e3 != cudaSuccess) { avr_set_error("streams: compaction failed (%d)", lrc ? lrc : (int)(e2 ? e2 : e3)); rc = AVR_E_CUDA; goto done; }
+  }
+  CU(cudaMemcpyAsync(coded_off, d_off, sizeof(uint64_t) * (nstreams + 1), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(status.data(), d_status, sizeof(int) * nstreams, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(len.data(), d_len, sizeof(uint32_t) * nstreams, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (uint32_t s = 0; s < nstreams; s++)
+    if (status[s]) { avr_set_error("streams: stream %u failed with %d (scratch %u bytes, wrote %u)", s, status[s], cap, len[s]); rc = status[s]; goto done; }
+  total = coded_off[nstreams];
+  coded->data = (uint8_t*)malloc(total ? total : 1);
+  if (!coded->data) { avr_set_error("streams: out of host memory"); rc = AVR_E_NOMEM; goto done; }
+  coded->size = total;
+  if (total) CU(cudaMemcpyAsync(coded->data, d_out, total, cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(ev[3], st));
+  CU(cudaStreamSynchronize(st));
+  if (t) {
+    t->h2d_ms = ev_ms(ev[0], ev[1]); t->kernel_ms = ev_ms(ev[1], ev[2]); t->d2h_ms = ev_ms(ev[2], ev[3]);
+    t->h2d_bytes = nbytes; t->d2h_bytes = total + (uint64_t)nstreams * 16 + 8;
+    t->bins = (uint64_t)nstreams * nbins; t->coded_symbols = t->bins; t->launches = 3;
+    t->coder_launch_ms_x1000 = (uint32_t)(t->kernel_ms * 1000.0);
+  }
+done:
+  if (rc && coded->data) { free(coded->data); coded->data = nullptr; coded->size = 0; }
+  cudaFree(d_bits); cudaFree(d_scratch); cudaFree(d_out); cudaFree(d_len); cudaFree(d_status); cudaFree(d_off); cudaFree(d_div);
+  for (auto& e : ev) if (e) cudaEventDestroy(e);
+  return rc;
+}
+
+extern "C" int avr_streams_decode(avr_context* ctx, const uint8_t* coded, const uint64_t* coded_off, uint32_t nstreams, uint32_t nbins,
+                                  int digit_bits, int model, uint8_t* bits_out, avr_timing* t) {
+  int rc = check_args(ctx, nstreams, nbins, digit_bits, model);
+  if (rc) return rc;
+  if (!coded_off || (nstreams && nbins && !bits_out)) { avr_set_error("streams: null argument"); return AVR_E_ARG; }
+  if (t) memset(t, 0, sizeof *t);
+  if (nstreams == 0 || nbins == 0) return AVR_OK;
+  for (uint32_t s = 0; s < nstreams; s++)
+    if (coded_off[s + 1] < coded_off[s] || coded_off[s + 1] - coded_off[s] > 0xFFFFFFFFull) { avr_set_error("streams: offsets not ascending at %u", s); return AVR_E_ARG; }
+  const uint64_t total = coded_off[nstreams];
+  if (total && !coded) { avr_set_error("streams: null argument"); return AVR_E_ARG; }
+  cudaStream_t st = (cudaStream_t)avr_context_stream(ctx);
+  const size_t nbytes = (size_t)nstreams * nbins;
+  uint8_t *d_coded = nullptr, *d_bits = nullptr; uint64_t* d_off = nullptr; AvrDivTab* d_div = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  const AvrDivTab h_div = AVR_DIV_TAB_INIT;
+  const uint32_t grid = (nstreams + AVR_STREAM_BLOCK - 1) / AVR_STREAM_BLOCK;
+  for (auto& e : ev) CU(cudaEventCreate(&e));
+  CU(cudaMalloc(&d_coded, total + 8));
+  CU(cudaMalloc(&d_bits, nbytes + 8));
+  CU(cudaMalloc(&d_off, sizeof(uint64_t) * (nstreams + 1)));
+  CU(cudaMalloc(&d_div, sizeof(AvrDivTab)));
+  CU(cudaEventRecord(ev[0], st));
+  CU(cudaMemcpyAsync(d_div, &h_div, sizeof h_div, cudaMemcpyHostToDevice, st));
+  if (total) CU(cudaMemcpyAsync(d_coded, coded, total, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_off, coded_off, sizeof(uint64_t) * (nstreams + 1), cudaMemcpyHostToDevice, st));
+  CU(cudaEventRecord(ev[1], st));
+#define LAUNCH_DEC(D, M) avr_k_stream_decode<D, M><<<grid, AVR_STREAM_BLOCK, 0, st>>>(d_coded, d_off, nstreams, nbins, d_div, d_bits)
+  if (digit_bits == 8) { if (model == AVR_STREAM_ADAPTIVE) LAUNCH_DEC(8, AVR_STREAM_ADAPTIVE); else LAUNCH_DEC(8, AVR_STREAM_FIXED_HALF); }
+  else { if (model == AVR_STREAM_ADAPTIVE) LAUNCH_DEC(16, AVR_STREAM_ADAPTIVE); else LAUNCH_DEC(16, AVR_STREAM_FIXED_HALF); }
+#undef LAUNCH_DEC
+  CU(cudaGetLastError());
+  CU(cudaEventRecord(ev[2], st));
+  CU(cudaMemcpyAsync(bits_out, d_bits, nbytes, cudaMemcpyDeviceToHost, st));
+  CU(cudaEventRecord(ev[3], st));
+  CU(cudaStreamSynchronize(st));
+  if (t) {
+    t->h2d_ms = ev_ms(ev[0], ev[1]); t->kernel_ms = ev_ms(ev[1], ev[2]); t->d2h_ms = ev_ms(ev[2], ev[3]);
+    t->h2d_bytes = total + (uint64_t)(nstreams + 1) * 8; t->d2h_bytes = nbytes;
+    t->bins = (uint64_t)nstreams * nbins; t->coded_symbols = t->bins; t->launches = 1;
+    t->coder_launch_ms_x1000 = (uint32_t)(t->kernel_ms * 1000.0);
+  }
+done:
+  cudaFree(d_coded); cudaFree(d_bits); cudaFree(d_off); cudaFree(d_div);
+  for (auto& e : ev) if (e) cudaEventDestroy(e);
+  return rc;
+}

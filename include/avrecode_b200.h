@@ -144,6 +144,19 @@ int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, const size_
                          avr_buffer* out, avr_timing* t);
 void avr_buffer_free(avr_buffer* b);
 
+/* ---- streams: the reference's coder test on S independent bin streams (test/arithmetic_code.cpp:93-110) ---- */
+/* bits: nstreams * nbins bytes, stream-major, one byte per bin (zero / non-zero).  digit_bits selects
+ * arithmetic_code<uint64_t,uint16_t> (16, the test's coder) or <uint64_t,uint8_t> (8, recode.cpp:322-323).
+ * model 0: p1 = range/2 (test/arithmetic_code.cpp:97); model 1: one adaptive estimator per stream,
+ * p1 = (range/(pos+neg))*pos with the counts of recode.cpp:1037-1054 (limit 0x60).
+ * coded = the streams' bytes back to back, coded_off[nstreams + 1] = where each begins (caller-allocated). */
+#define AVR_STREAM_FIXED_HALF 0
+#define AVR_STREAM_ADAPTIVE 1
+int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_t nstreams, uint32_t nbins, int digit_bits, int model,
+                       avr_buffer* coded, uint64_t* coded_off, avr_timing* t);
+int avr_streams_decode(avr_context* ctx, const uint8_t* coded, const uint64_t* coded_off, uint32_t nstreams, uint32_t nbins,
+                       int digit_bits, int model, uint8_t* bits_out, avr_timing* t);
+
 #ifdef __cplusplus
 }
 #endif

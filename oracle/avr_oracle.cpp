@@ -27,6 +27,8 @@
 //        sequence only (symbols are used to verify), prints "C <hex>" = re-encoded CABAC bytes
 //        per slice and "OK bins=<n>" or "MISMATCH ..." (exit 1)
 //   avr_oracle bench <trace> <reps>           times encode and decode, prints Mbins/s
+//   avr_oracle streams <digit_bits> <model> <nstreams> <nbins> <bits file> [quiet]
+//        BASELINE configs[0]: the coder test of test/arithmetic_code.cpp:93-110 per stream; prints "A <hex>"
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -114,6 +116,122 @@ struct RangeDecoder64 {
     return symbol;
   }
 };
+
+// ---------------------------------------------------------------------------------------
+// The same coder for any digit width (test/arithmetic_code.cpp:93 uses <uint64_t,uint16_t>): put-time digits are
+// Digit wide and leave as bytes MSB first (arithmetic_code.h:185-190); finish() flushes 8-bit digits
+// (renormalize_and_emit_digit<OutputDigit>, arithmetic_code.h:139-142); `overflow` holds Digit-wide entries.
+// ---------------------------------------------------------------------------------------
+template <typename Digit>
+struct RangeEncoderT {
+  static constexpr uint64_t fixed_one = 1ull << 63;
+  static constexpr uint64_t base = 1ull << (8 * sizeof(Digit));
+  static constexpr uint64_t min_range = (fixed_one / base) / 16;
+  uint64_t low = 0, range = fixed_one;
+  std::vector<Digit> overflow;
+  std::vector<uint8_t>* out;
+  explicit RangeEncoderT(std::vector<uint8_t>* o) : out(o) {}
+  void emit(Digit d) { for (int i = (int)sizeof(Digit) - 1; i >= 0; i--) out->push_back((uint8_t)(d >> (8 * i))); }
+  void put(int symbol, uint64_t range_of_1) {
+    uint64_t range_of_0 = range - range_of_1;
+    if (symbol) { low += range_of_0; range = range_of_1; } else { range = range_of_0; }
+    if (range < min_range) {
+      if (range == 0) { fprintf(stderr, "zero-probability symbol\n"); exit(2); }
+      while (range < fixed_one / base) renorm<Digit>();
+    }
+  }
+  template <typename D>
+  void renorm() {                                                  // arithmetic_code.h:148-180 with Digit = D
+    const uint64_t b = 1ull << (8 * sizeof(D)), msd = fixed_one / b;
+    if (low >= fixed_one) {
+      for (int i = (int)overflow.size() - 1; i >= 0; i--) if (++overflow[i] != 0) break;
+      low -= fixed_one;
+    }
+    D digit = (D)(low / msd);
+    if (digit != (D)((low + range - 1) / msd)) {
+      overflow.push_back(digit);                                   // stored as CompressedDigit
+    } else {
+      for (Digit d : overflow) emit(d);                            // emit_digit(CompressedDigit)
+      overflow.clear();
+      for (int i = (int)sizeof(D) - 1; i >= 0; i--) out->push_back((uint8_t)(digit >> (8 * i)));
+    }
+    low -= digit * msd;
+    low *= b;
+    range *= b;
+  }
+  void finish() {
+    for (uint64_t stop = fixed_one >> 1; stop > 0; stop >>= 1) {
+      uint64_t x = (low | stop) & ~(stop - 1);
+      if (stop < range && low <= x && x < low + range) { low = x; break; }
+    }
+    while (low != 0) { range = 1; renorm<uint8_t>(); }
+    range = 0;
+  }
+};
+template <typename Digit>
+struct RangeDecoderT {
+  static constexpr uint64_t fixed_one = 1ull << 63;
+  static constexpr uint64_t base = 1ull << (8 * sizeof(Digit));
+  static constexpr uint64_t min_range = (fixed_one / base) / 16;
+  const uint8_t* in; const uint8_t* end;
+  Digit next_digit;
+  uint64_t low, range;
+  RangeDecoderT(const uint8_t* b, const uint8_t* e) : in(b), end(e) {
+    next_digit = aligned();
+    low = next_digit / 2;
+    range = base / 2;
+    while (range < fixed_one) consume();
+  }
+  Digit aligned() {                                                // arithmetic_code.h:278-287
+    Digit d = 0;
+    for (int i = (int)sizeof(Digit) - 1; i >= 0; i--) { d = (Digit)(d * 256); if (in != end) d |= *in++; }
+    return d;
+  }
+  void consume() {
+    Digit d = aligned();
+    Digit digit = (Digit)((next_digit * (base / 2)) | (d / 2));
+    next_digit = d;
+    low = low * base + digit;
+    range *= base;
+  }
+  int get(uint64_t range_of_1) {
+    uint64_t range_of_0 = range - range_of_1;
+    int symbol = low >= range_of_0;
+    if (symbol) { low -= range_of_0; range = range_of_1; } else { range = range_of_0; }
+    if (range < min_range) while (range < fixed_one / base) consume();
+    return symbol;
+  }
+};
+struct StreamCounts {                                              // recode.cpp:1064, 1037-1054 (limit 0x60), 823-827
+  int pos = 1, neg = 1;
+  uint64_t p1(uint64_t range) const { return (range / (uint64_t)(pos + neg)) * (uint64_t)pos; }
+  void update(int symbol) {
+    if (symbol) pos++; else neg++;
+    if (pos + neg > 0x60) { pos = (pos + 1) / 2; neg = (neg + 1) / 2; }
+  }
+};
+// test/arithmetic_code.cpp:93-110 for one stream; model 0 = `range/2`, model 1 = adaptive counts
+template <typename Digit>
+static bool stream_roundtrip(int model, const uint8_t* bits, long nbins, std::vector<uint8_t>* out) {
+  {
+    RangeEncoderT<Digit> enc(out);
+    StreamCounts c;
+    for (long i = 0; i < nbins; i++) {
+      int bit = bits[i] != 0;
+      enc.put(bit, model == 0 ? enc.range / 2 : c.p1(enc.range));
+      if (model) c.update(bit);
+    }
+    enc.finish();
+  }
+  RangeDecoderT<Digit> dec(out->data(), out->data() + out->size());
+  StreamCounts c;
+  for (long i = 0; i < nbins; i++) {
+    int bit = dec.get(model == 0 ? dec.range / 2 : c.p1(dec.range));
+    if (model) c.update(bit);
+    if (bit != (bits[i] != 0)) return false;
+  }
+  return true;
+}
 
 // ---------------------------------------------------------------------------------------
 // CABAC encoder = arithmetic_code<uint32_t,uint16_t,0x200>::encoder<..., uint8_t>
@@ -541,6 +659,30 @@ static bool load_payloads(const char* fn, std::vector<std::vector<uint8_t>>* p) 
 }
 
 int main(int argc, char** argv) {
+  if (argc >= 7 && std::string(argv[1]) == "streams") {
+    // avr_oracle streams <digit_bits> <model> <nstreams> <nbins> <bits file> [quiet]: "A <hex>" per stream
+    const int digit_bits = atoi(argv[2]), model = atoi(argv[3]);
+    const long nstreams = atol(argv[4]), nbins = atol(argv[5]);
+    const bool quiet = argc >= 8;
+    std::vector<uint8_t> bits((size_t)(nstreams * nbins));
+    FILE* f = fopen(argv[6], "rb");
+    if (!f || fread(bits.data(), 1, bits.size(), f) != bits.size()) { fprintf(stderr, "cannot read %s\n", argv[6]); return 2; }
+    fclose(f);
+    auto t0 = std::chrono::steady_clock::now();
+    uint64_t bytes = 0;
+    for (long s = 0; s < nstreams; s++) {
+      std::vector<uint8_t> out;
+      const bool ok = digit_bits == 16 ? stream_roundtrip<uint16_t>(model, bits.data() + s * nbins, nbins, &out)
+                                       : stream_roundtrip<uint8_t>(model, bits.data() + s * nbins, nbins, &out);
+      if (!ok) { fprintf(stderr, "stream %ld does not round-trip\n", s); return 1; }
+      bytes += out.size();
+      if (!quiet) print_hex("A ", out);
+    }
+    double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (quiet) printf("{\"bins\": %lld, \"bytes\": %llu, \"roundtrip_s\": %.6f, \"mbins_s\": %.3f}\n", (long long)(nstreams * nbins),
+                      (unsigned long long)bytes, sec, nstreams * nbins / sec / 1e6);
+    return 0;
+  }
   if (argc < 3) { fprintf(stderr, "usage: %s encode <trace> | decode <trace> <payloads> [--ref-quirks] | bench <trace> <reps>\n", argv[0]); return 2; }
   std::string cmd = argv[1];
   Trace tr;

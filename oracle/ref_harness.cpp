@@ -14,6 +14,14 @@
 //   B cat n max_coeff is_dc c422   (begin_sub_mb observed)
 //   [ / ]                      (begin/end_coding_type SIGNIFICANCE_MAP)
 //   c <ctxIdx> <sym> | b <sym> | t <sym>
+//   ref_harness arith <digit_bits 8|16> <model 0|1> <nstreams> <nbins> <bits file>
+//                                      : the reference's arithmetic_code<uint64_t,Digit> exactly as
+//                                        test/arithmetic_code.cpp:93-110 drives it (make_encoder over a
+//                                        vector<uint8_t>, put(bit, lambda), finish, make_decoder, get), one
+//                                        stream after the other; model 0 = the test's `range/2`, model 1 = one
+//                                        adaptive estimator per stream with recode.cpp's counts (:823-827,
+//                                        :1037-1054).  Prints "A <hex>" per stream, exit 1 if its own decoder
+//                                        does not return the bits.
 #define main recode_main
 #include "recode.cpp"
 #undef main
@@ -104,7 +112,54 @@ class tracer {
   h264_model model;
 };
 
+struct arith_counts {                      // estimator of recode.cpp:1064 with the update of :1037-1054 (limit 0x60)
+  int pos = 1, neg = 1;
+  void update(int symbol) {
+    if (symbol) pos++; else neg++;
+    if (pos + neg > 0x60) { pos = (pos + 1) / 2; neg = (neg + 1) / 2; }
+  }
+};
+template <typename Digit>
+static int arith_streams(int model, long nstreams, long nbins, const std::vector<uint8_t>& bits) {
+  typedef arithmetic_code<uint64_t, Digit> code;
+  for (long s = 0; s < nstreams; s++) {
+    const uint8_t* b = bits.data() + s * nbins;
+    std::vector<uint8_t> out;
+    {
+      auto encoder = make_encoder<code>(&out);
+      arith_counts c;
+      for (long i = 0; i < nbins; i++) {
+        int bit = b[i] != 0;
+        if (model == 0) encoder.put(bit, [](uint64_t range) { return range / 2; });
+        else { encoder.put(bit, [&c](uint64_t range) { return (range / (c.pos + c.neg)) * c.pos; }); c.update(bit); }
+      }
+      encoder.finish();
+    }
+    printf("A ");
+    for (uint8_t x : out) printf("%02x", x);
+    printf("\n");
+    auto decoder = make_decoder<code>(out);
+    arith_counts c;
+    for (long i = 0; i < nbins; i++) {
+      int bit;
+      if (model == 0) bit = decoder.get([](uint64_t range) { return range / 2; });
+      else { bit = decoder.get([&c](uint64_t range) { return (range / (c.pos + c.neg)) * c.pos; }); c.update(bit); }
+      if (bit != (b[i] != 0)) { fprintf(stderr, "stream %ld: mismatch at bit %ld\n", s, i); return 1; }
+    }
+  }
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc >= 7 && std::string(argv[1]) == "arith") {
+    const int digit_bits = atoi(argv[2]), model = atoi(argv[3]);
+    const long nstreams = atol(argv[4]), nbins = atol(argv[5]);
+    std::vector<uint8_t> bits((size_t)(nstreams * nbins));
+    FILE* f = fopen(argv[6], "rb");
+    if (!f || fread(bits.data(), 1, bits.size(), f) != bits.size()) { fprintf(stderr, "cannot read %s\n", argv[6]); return 2; }
+    fclose(f);
+    return digit_bits == 16 ? arith_streams<uint16_t>(model, nstreams, nbins, bits) : arith_streams<uint8_t>(model, nstreams, nbins, bits);
+  }
   av_register_all();
   av_log_set_level(AV_LOG_ERROR);
   if (argc >= 3 && std::string(argv[1]) == "trace") {
@@ -117,6 +172,6 @@ int main(int argc, char** argv) {
     }
     return 0;
   }
-  fprintf(stderr, "usage: %s trace <file>\n", argv[0]);
+  fprintf(stderr, "usage: %s trace <file> | arith <digit_bits> <model> <nstreams> <nbins> <bits file>\n", argv[0]);
   return 1;
 }

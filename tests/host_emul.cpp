@@ -15,6 +15,7 @@
 #include "../avrecode-ms_b200/csrc/avr_pipeline.h"
 #include "../avrecode-ms_b200/csrc/avr_decode.h"
 #include "../avrecode-ms_b200/csrc/avr_parse.h"
+#include "../avrecode-ms_b200/csrc/avr_streams.h"
 #include <algorithm>
 
 static bool read_file(const char* fn, std::vector<uint8_t>* out) {
@@ -252,7 +253,39 @@ static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& 
   return ok ? 0 : 1;
 }
 
+// streams <digit_bits> <model> <nstreams> <nbins> <bits file>: the stream kernels' bodies (avr_streams.h) as an emulated grid:
+// encode every stream into its scratch, compact, decode from the compacted buffer, compare; prints "A <hex>" per stream
+template <int D, int M>
+static int streams_emul(uint32_t nstreams, uint32_t nbins, const std::vector<uint8_t>& bits) {
+  const AvrDivTab dt = AVR_DIV_TAB_INIT;
+  const uint32_t cap = avr_stream_cap(nbins, M);
+  std::vector<uint8_t> scratch((size_t)nstreams * cap + 8), coded, back(bits.size() + 8);
+  std::vector<uint32_t> len(nstreams); std::vector<int> status(nstreams);
+  std::vector<uint64_t> off(nstreams + 1, 0);
+  for (uint32_t s = 0; s < nstreams; s++) avr_body_stream_encode<D, M>(s, bits.data(), nbins, &dt, scratch.data(), cap, len.data(), status.data());
+  for (uint32_t s = 0; s < nstreams; s++) {
+    if (status[s]) { fprintf(stderr, "stream %u: status %d\n", s, status[s]); return 1; }
+    off[s + 1] = off[s] + len[s];
+    coded.insert(coded.end(), scratch.begin() + (size_t)s * cap, scratch.begin() + (size_t)s * cap + len[s]);
+    print_hex("A ", scratch.data() + (size_t)s * cap, len[s]);
+  }
+  coded.resize(coded.size() + 8);
+  for (uint32_t s = 0; s < nstreams; s++) avr_body_stream_decode<D, M>(s, coded.data(), off.data(), nbins, &dt, back.data());
+  for (size_t i = 0; i < bits.size(); i++) if ((bits[i] != 0) != (back[i] != 0)) { fprintf(stderr, "decode mismatch at %zu\n", i); return 1; }
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc >= 7 && std::string(argv[1]) == "streams") {
+    const int d = atoi(argv[2]), m = atoi(argv[3]);
+    const uint32_t ns = (uint32_t)atol(argv[4]), nb = (uint32_t)atol(argv[5]);
+    std::vector<uint8_t> bits;
+    if (!read_file(argv[6], &bits) || bits.size() != (size_t)ns * nb) { fprintf(stderr, "cannot read %s\n", argv[6]); return 2; }
+    bits.resize(bits.size() + 8);   // word reads of the last row stay inside the buffer
+    std::vector<uint8_t> view(bits.begin(), bits.end() - 8);
+    if (d == 16) return m ? streams_emul<16, 1>(ns, nb, view) : streams_emul<16, 0>(ns, nb, view);
+    return m ? streams_emul<8, 1>(ns, nb, view) : streams_emul<8, 0>(ns, nb, view);
+  }
   if (argc < 3) { fprintf(stderr, "usage: %s chain|pipeline|roundtrip <clip>\n", argv[0]); return 2; }
   std::string cmd = argv[1];
   std::vector<uint8_t> data;
