@@ -59,7 +59,7 @@ static AVR_HD uint32_t avr_nz_bit_key(const AvrNzCtx& c, int i, int so_far) {
   int bit = 1 << i;
   int lb = c.has_left ? (c.left_nz >= bit) : 2;
   int ab = c.above_nz ? (c.above_nz >= bit) : 2;      // sic: tests the count, not has_above (recode.cpp:888)
-  return avr_key_nz(i, so_far, c.prev_nz >= bit, lb, ab, c.third);
+  return avr_key_nz(i, so_far & (bit - 1), c.prev_nz >= bit, lb, ab, c.third);   // so_far < 2^i by construction; the mask keeps prefetch keys inside the line
 }
 // cur / prev = base of the 64-byte-per-MB stores of the current and previous picture (prev may
 // be null = all zero).  Only valid after the block's own is_8x8 contribution has been stored.

@@ -62,13 +62,17 @@ typedef struct AvrFrame {
 // default keys   : [0, 1026)                    key = ctx code
 // sig-map keys   : AVR_KEY_SIG_BASE + ((cat*64 + nnz)*64 + obs)*16 + zz_off
 //                  cat<14, nnz<64 (stored count, recode.cpp:928-931), obs<64, zz_off<16
-// nnz-bit keys   : AVR_KEY_NZ_BASE + (((i*64 + so_far)*18 + nb18)*64 + third)
-//                  i<6, so_far<64, nb18 = prev + 2*left + 6*above (each of left/above in 0..2),
-//                  third = is_8x8 + 2*is_dc + c422 + 4*cat  (<64)
-#define AVR_KEY_SIG_BASE 1026u
+//                  one (cat, nnz, obs) row = 16 cells = one 32-byte sector: a block walks its rows in order
+// nnz-bit keys   : AVR_KEY_NZ_BASE + ((third*18 + nb18)*64 + (2^i + so_far))
+//                  third = is_8x8 + 2*is_dc + c422 + 4*cat  (<64), nb18 = prev + 2*left + 6*above (each of
+//                  left/above in 0..2), i<6, so_far<2^i: level i of a count's bit tree is the 2^i cells that start at
+//                  cell 2^i of the line (naturally aligned, so a level is ONE 2/4/8/16-byte load; cell 0 unused);
+//                  a 4-bit count stays inside one sector per neighbour class instead of 6 planes
+// Bases are multiples of 64 cells and the per-file pool is a multiple of 128 bytes, so rows never straddle sectors.
+#define AVR_KEY_SIG_BASE 1088u
 #define AVR_KEY_SIG_COUNT (14u * 64u * 64u * 16u)
 #define AVR_KEY_NZ_BASE (AVR_KEY_SIG_BASE + AVR_KEY_SIG_COUNT)
-#define AVR_KEY_NZ_COUNT (6u * 64u * 18u * 64u)
+#define AVR_KEY_NZ_COUNT (64u * 18u * 64u)
 #define AVR_KEY_COUNT (AVR_KEY_NZ_BASE + AVR_KEY_NZ_COUNT)
 #define AVR_KEY_BITS 21
 
@@ -76,7 +80,7 @@ static AVR_HD uint32_t avr_key_sig(int cat, int nnz_stored, int obs, int zz_off)
   return AVR_KEY_SIG_BASE + ((((uint32_t)cat * 64u + (uint32_t)nnz_stored) * 64u + (uint32_t)obs) * 16u + (uint32_t)zz_off);
 }
 static AVR_HD uint32_t avr_key_nz(int i, int so_far, int prev, int left, int above, int third) {
-  return AVR_KEY_NZ_BASE + (((((uint32_t)i * 64u + (uint32_t)so_far) * 18u + (uint32_t)(prev + 2 * left + 6 * above)) * 64u) + (uint32_t)third);
+  return AVR_KEY_NZ_BASE + (((uint32_t)third * 18u + (uint32_t)(prev + 2 * left + 6 * above)) * 64u + ((1u << i) + (uint32_t)so_far));
 }
 // halving threshold by key class (reference recode.cpp:1048-1049): sig-map keys 0x50, all others 0x60
 static AVR_HD int avr_key_is_sig(uint32_t key) { return key >= AVR_KEY_SIG_BASE && key < AVR_KEY_NZ_BASE; }

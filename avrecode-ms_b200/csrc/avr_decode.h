@@ -53,7 +53,6 @@ struct AvrDecShared {
   uint8_t* store[2];
   int cur, mb_w;
   uint32_t mb_addr, mb_x;
-  uint32_t bins;
   int done;
   uint64_t self;                               // shared-window address of this object, read back as an opaque value (see avr_sbase)
 };
@@ -344,12 +343,13 @@ AVR_DEC_INL int avr_dec_single(uint32_t key) {
   uint32_t u0, u1; avr_cell_update2(e.cell, 0x60, u0, u1);
   const int sym = avr_dec_core(low, range, e);
   avr_s_st16(a, sym ? u1 : u0);
-  avr_ring_reserve(head, tail_seen, 1);
+#if defined(__CUDACC__)
+  if (head - tail_seen >= AVR_RING - 1) { avr_ring_reserve(head, tail_seen, 1); g_dec.ring_tail_seen = tail_seen; }   // rare: ring full
+#endif
   avr_ring_store(s_ring, head, (key << 1) | (uint32_t)sym);
   AVR_DEC_RENORM(low, range);
   g_dec.low = low; g_dec.range = range;
-  g_dec.ring_head = head + 1; g_dec.ring_tail_seen = tail_seen;
-  g_dec.bins++;
+  g_dec.ring_head = head + 1;                                    // every bin posts one record: bins of the slice = head delta
   return sym;
 }
 AVR_DEC_FN int avr_dec_get(int ctx) { return avr_dec_single((uint32_t)ctx); }
@@ -408,7 +408,6 @@ AVR_DEC_INL int avr_dec_sigmap(uint64_t& low, uint64_t& range, uint32_t& head, u
 AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, int sig_base, int last_base, int abs_base) {
   uint64_t low = g_dec.low, range = g_dec.range;
   uint32_t head = g_dec.ring_head, tail_seen = g_dec.ring_tail_seen;
-  const uint32_t head0 = head;                                   // every bin of the block is posted once: bins = head - head0
   uint16_t* const est = g_dec.est;
   const avr_sptr s_base = avr_sbase();
   const avr_sptr s_ms = s_base + AVR_S_OFF(ms), s_ring = s_base + AVR_S_OFF(ring), s_def = s_base + AVR_S_OFF(est_def);
@@ -512,7 +511,6 @@ AVR_DEC_FN int avr_dec_residual_block(int cat, int n, int max_coeff, int is_dc, 
   avr_s_st16(a_byp, byp.cell);
   g_dec.low = low; g_dec.range = range;
   g_dec.ring_head = head; g_dec.ring_tail_seen = tail_seen;
-  g_dec.bins += head - head0;
   return coeff_count;
 }
 
@@ -548,12 +546,13 @@ AVR_DEC_INL void avr_dec_flip_zero(const AvrDecSlice& ds, int lane, int nlanes) 
 AVR_DEC_FN int avr_dec_slice(const AvrDecSlice& ds, const uint8_t* payloads, avr::MbInfo* row, uint32_t uid, uint32_t* out_bins) {
   if (uid == 1) for (int x = 0; x < ds.sp.mb_w; x++) row[x].uid = 0;
   avr_dec_init_range(payloads + ds.payload_off, ds.payload_len);
-  g_dec.bins = 0; g_dec.done = 0; g_dec.mb_addr = 0;
+  g_dec.done = 0; g_dec.mb_addr = 0;
+  const uint32_t head0 = g_dec.ring_head;                      // every bin posts exactly one record
   AvrDecPolicy io;
   avr::SliceParser<AvrDecPolicy> parser(io, ds.sp, row, uid);
   const int rc = parser.run();
+  *out_bins = g_dec.ring_head - head0;
   if (!g_dec.done) avr_ring_post(AVR_REC_ABORT, 0);            // release the encoder thread
-  *out_bins = g_dec.bins;
   return rc < 0 ? AVR_E_CORRUPT : !g_dec.done ? AVR_E_CORRUPT : g_dec.pos > ds.payload_len + 16 ? AVR_E_CORRUPT : AVR_OK;
 }
 

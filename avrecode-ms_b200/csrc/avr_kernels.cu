@@ -5,6 +5,7 @@
 // strict per-bin dependency), the other lanes help with bulk work (zeroing the
 // picture store, CABAC state init).  Slice-parallel compress pipeline: see avr_pipeline.h.
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include "avr_bodies.h"
 #include "avr_kernels.h"
 #include "avr_pipeline.h"
@@ -160,6 +161,24 @@ int avr_launch_compress_chain(const AvrDevBatch& b, cudaStream_t st) {
 
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
   if (b.nfiles == 0) return 0;
+  {
+    // L1 and shared memory are one 256 KB array per SM.  Left alone the driver carves out shared memory for as many
+    // blocks as registers allow (14 x 10 KB), which leaves the chains' estimator cells ~90 KB of L1; a batch that puts
+    // fewer chains on an SM asks only for what those need, the rest stays L1 (profiles/r01_contention.md).
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaFuncAttributes fa;
+    int pct = -1;
+    if (const char* e = getenv("AVR_DEC_CARVEOUT")) pct = atoi(e);
+    else if (cudaFuncGetAttributes(&fa, avr_k_decompress_chain) == cudaSuccess) {
+      const int per_sm = (b.nfiles + sms - 1) / sms;
+      const size_t need = (size_t)per_sm * (fa.sharedSizeBytes + 1024);      // + the per-block reservation
+      pct = (int)((need * 100 + 233471) / 233472);
+      if (pct > 100) pct = 100;
+    }
+    if (pct >= 0) cudaFuncSetAttribute(avr_k_decompress_chain, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+  }
   avr_k_decompress_chain<<<b.nfiles, AVR_DEC_THREADS, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
                                                  b.tab, b.out, b.out_len, b.out_bins, b.status, b.file_order);
   return (int)cudaGetLastError();

@@ -19,6 +19,9 @@ AVR_MEM_INL uint64_t avr_s_ld64_ro(avr_sptr a) { uint64_t v; asm("ld.shared.u64 
 AVR_MEM_INL void avr_s_ld_2x64_ro(avr_sptr a, uint64_t& x, uint64_t& y) { asm("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "r"(a)); }
 AVR_MEM_INL uint32_t avr_g_ld16(const uint16_t* p) { uint16_t v; asm volatile("ld.global.u16 %0, [%1];" : "=h"(v) : "l"(p) : "memory"); return v; }
 AVR_MEM_INL void avr_g_st16(uint16_t* p, uint32_t v) { asm volatile("st.global.u16 [%0], %1;" ::"l"(p), "h"((uint16_t)v) : "memory"); }
+AVR_MEM_INL uint32_t avr_g_ld32(const void* p) { uint32_t v; asm volatile("ld.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+AVR_MEM_INL uint64_t avr_g_ld64(const void* p) { uint64_t v; asm volatile("ld.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); return v; }
+AVR_MEM_INL void avr_g_ld_2x64(const void* p, uint64_t& x, uint64_t& y) { asm volatile("ld.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(p) : "memory"); }
 #else
 #if defined(__CUDACC__)
 #define AVR_MEM_INL static __device__ __forceinline__
@@ -36,4 +39,7 @@ AVR_MEM_INL uint64_t avr_s_ld64_ro(avr_sptr a) { return *reinterpret_cast<const 
 AVR_MEM_INL void avr_s_ld_2x64_ro(avr_sptr a, uint64_t& x, uint64_t& y) { const uint64_t* e = reinterpret_cast<const uint64_t*>(a); x = e[0]; y = e[1]; }
 AVR_MEM_INL uint32_t avr_g_ld16(const uint16_t* p) { return *p; }
 AVR_MEM_INL void avr_g_st16(uint16_t* p, uint32_t v) { *p = (uint16_t)v; }
+AVR_MEM_INL uint32_t avr_g_ld32(const void* p) { const uint16_t* q = reinterpret_cast<const uint16_t*>(p); return q[0] | ((uint32_t)q[1] << 16); }
+AVR_MEM_INL uint64_t avr_g_ld64(const void* p) { return avr_g_ld32(p) | ((uint64_t)avr_g_ld32(reinterpret_cast<const uint16_t*>(p) + 2) << 32); }
+AVR_MEM_INL void avr_g_ld_2x64(const void* p, uint64_t& x, uint64_t& y) { x = avr_g_ld64(p); y = avr_g_ld64(reinterpret_cast<const uint16_t*>(p) + 4); }
 #endif

@@ -252,6 +252,33 @@ def main():
                       "note": "decompress of ONE file is a single sequential chain (SURVEY 7.0)"}
             c1.close(); d1.close(); r1.close()
 
+        # ---- BASELINE configs[0]: independent bin streams through the generic range coder (plumbing config) ----
+        streams = None
+        if rank == 0 and not args.no_single:
+            import numpy as np
+            S, N = 8192, 16384
+            rng = np.random.RandomState(1)
+            pr = np.array([0.5, 0.1, 0.01, 0.001])[np.arange(S) % 4][:, None]
+            sbits = (rng.random_sample((S, N)) < pr).astype(np.uint8)
+            raw = sbits.tobytes()
+            streams = {"workload": f"config1: {S} streams x {N} bins, p(1) in 0.5/0.1/0.01/0.001, host buffers in and out", "runs": []}
+            for digit_bits, model, name in ((16, 0, "u64/u16 p1=range/2 (test/arithmetic_code.cpp)"), (8, 1, "u64/u8 adaptive counts (recode.cpp estimator)")):
+                A.streams_encode(ctx, raw, S, N, digit_bits, model)
+                coded, te = A.streams_encode(ctx, raw, S, N, digit_bits, model)
+                back, tdn = A.streams_decode(ctx, coded, S, N, digit_bits, model)
+                assert back == raw, "stream roundtrip is not bit-exact"
+                streams["runs"].append({"coder": name, "encode_gbins_s": S * N / te["kernel_ms"] / 1e6, "decode_gbins_s": S * N / tdn["kernel_ms"] / 1e6,
+                                        "coded_bytes": sum(len(c) for c in coded), "bit_exact": True})
+            # the CPU restatement of the same test on one host core, bounded sample (first 256 streams)
+            sp = os.path.join(td, "streams.bin")
+            with open(sp, "wb") as f:
+                f.write(sbits[:256].tobytes())
+            try:
+                o = subprocess.run([os.path.join(REF, "avr_oracle"), "streams", "16", "0", "256", str(N), sp, "quiet"], stdout=subprocess.PIPE, check=True).stdout
+                streams["cpu_port_1core_mbins_s"] = json.loads(o)["mbins_s"]
+            except (OSError, subprocess.CalledProcessError, ValueError):
+                streams["cpu_port_1core_mbins_s"] = None
+
     # ---- max over ranks ----
     if world > 1:
         t = torch.tensor([dev_s, e2e_s], device="cuda", dtype=torch.float64)
@@ -302,6 +329,7 @@ def main():
                                         "compress_coder": 32 * bins / (coder_us / 1e6 / args.steps) / int_peak,
                                         "note": "planning ops/bin (SURVEY 8d) / (148 SM x 128 lanes x SM clock)"}},
         "single_clip": single,
+        "streams": streams,
     }
     if single:
         # what actually bounds the dominant kernel: the dependent-issue latency of ONE thread per file
