@@ -310,7 +310,15 @@ int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t
                      cudaStream_t st) {
   if (n == 0) return 0;
   avr_k_patch_tails<<<(n + 127) / 128, 128, 0, st>>>(ps, n, raw);
-  avr_k_parse<<<n, 32, 0, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
+  // Registers allow 28 one-warp blocks per SM, but with that many walkers at different places of the syntax code the
+  // kernel waits for instruction fetch (ncu on the bench corpus: stall no_instruction 34 %, profiles/r01_summary.md).
+  // Unused dynamic shared memory caps the residency at 12 per SM when the grid is large enough to fill the SMs that
+  // deep anyway: 148 -> 138 ms on 9 537 slices (8 per SM: 137, 5 per SM: 184).
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const size_t dyn = n > (uint32_t)sms * 12u ? 16000 : 0;
+  avr_k_parse<<<n, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
   return (int)cudaGetLastError();
 }
 int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,

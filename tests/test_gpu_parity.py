@@ -206,9 +206,10 @@ def test_large_roundtrip_property(ctx, tmpdir_path):
 @pytest.mark.parametrize("shape", [
     dict(seed=61, mb_w=240, mb_h=135, frames=2, slices_per_frame=68, p_sig=150, p_cbf=230, p_cbp=240, transform_8x8=1),   # config 5: 2160p, 68 slices/frame, dense residuals
     dict(seed=62, mb_w=120, mb_h=68, frames=12, slices_per_frame=8, num_ref=3),                                          # config 3: 1080p, 8 slices/frame
+    dict(seed=2, mb_w=120, mb_h=68, frames=5, slices_per_frame=1),                                                       # config 2: 1080p, 1 slice/frame
 ])
 def test_baseline_config_shapes_roundtrip(ctx, tmpdir_path, shape):
-    """BASELINE configs[2] / configs[4] picture and slice geometry (fewer frames): roundtrip == input, device parse ==
+    """BASELINE configs[1] / configs[2] / configs[4] picture and slice geometry (fewer frames): roundtrip == input, device parse ==
     host parse, pipeline == chain"""
     import avr_ctypes as A
     data = gen_clip(os.path.join(tmpdir_path, "cfg.h264"), **shape)
