@@ -1,6 +1,7 @@
 // avrbench: native timing / profiling harness over the C ABI (no Python in the process, so it can
 // run under ncu and compute-sanitizer).
 //   avrbench <reps> <mode: 0 pipeline | 1 chain | 2 decompress only | 3 file API (device parse)> <clip.h264>...
+//   avrbench <reps> 4 <streams> <bins> <digit_bits 8|16> <model 0|1>     coder test on independent bin streams (config 1)
 // Stages the clips' records once, runs compress `reps` times, stages the payloads, runs
 // decompress `reps` times, verifies the re-encoded CABAC bytes against the input files and
 // prints one line of JSON with the CUDA-event times.
@@ -25,6 +26,34 @@ static bool read_file(const char* fn, std::vector<uint8_t>* out) {
 int main(int argc, char** argv) {
   if (argc < 4) { fprintf(stderr, "usage: %s <reps> <mode> <clip>...\n", argv[0]); return 2; }
   const int reps = atoi(argv[1]), mode = atoi(argv[2]);
+  if (mode == 4) {
+    if (argc < 7) { fprintf(stderr, "usage: %s <reps> 4 <streams> <bins> <digit_bits> <model>\n", argv[0]); return 2; }
+    const uint32_t S = (uint32_t)atol(argv[3]), N = (uint32_t)atol(argv[4]);
+    const int digit_bits = atoi(argv[5]), model = atoi(argv[6]);
+    std::vector<uint8_t> bits((size_t)S * N), back((size_t)S * N);
+    uint64_t x = 88172645463325252ull;                       // xorshift64; p(1) cycles through 1/2, 1/8, 1/64, 1/1024 by stream
+    for (uint32_t s = 0; s < S; s++) {
+      static const int k[4] = {1, 3, 6, 10};
+      for (uint32_t i = 0; i < N; i++) { x ^= x << 13; x ^= x >> 7; x ^= x << 17; bits[(size_t)s * N + i] = (x >> 20 & ((1u << k[s & 3]) - 1)) == 0; }
+    }
+    avr_context* ctx;
+    CHECK(avr_context_create(0, &ctx));
+    std::vector<uint64_t> off((size_t)S + 1);
+    avr_timing te, td; double e_ms = 0, d_ms = 0; uint64_t coded_bytes = 0; int bad = 0;
+    for (int r = 0; r < reps; r++) {
+      avr_buffer coded;
+      CHECK(avr_streams_encode(ctx, bits.data(), S, N, digit_bits, model, &coded, off.data(), &te));
+      CHECK(avr_streams_decode(ctx, coded.data, off.data(), S, N, digit_bits, model, back.data(), &td));
+      e_ms += te.kernel_ms; d_ms += td.kernel_ms; coded_bytes = coded.size;
+      bad += memcmp(back.data(), bits.data(), bits.size()) != 0;
+      avr_buffer_free(&coded);
+    }
+    printf("{\"streams\": %u, \"bins_per_stream\": %u, \"digit_bits\": %d, \"model\": %d, \"coded_bytes\": %llu, \"encode_ms\": %.3f, "
+           "\"decode_ms\": %.3f, \"encode_gbins_s\": %.2f, \"decode_gbins_s\": %.2f, \"bad\": %d}\n", S, N, digit_bits, model,
+           (unsigned long long)coded_bytes, e_ms / reps, d_ms / reps, (double)S * N / 1e6 / (e_ms / reps), (double)S * N / 1e6 / (d_ms / reps), bad);
+    avr_context_destroy(ctx);
+    return bad ? 1 : 0;
+  }
   const int n = argc - 3;
   std::vector<std::vector<uint8_t>> data((size_t)n);
   std::vector<avr_record*> recs((size_t)n);

@@ -119,9 +119,13 @@ __global__ void __launch_bounds__(1024) avr_k_exclusive_scan_u32(const uint32_t*
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (uint32_t base = 0; base < n; base += 1024) {
-    uint32_t i = base + threadIdx.x;
-    uint64_t v = i < n ? len[i] : 0, x = v;
+  for (uint32_t base = 0; base < n; base += 4096) {            // four elements per thread and step
+    const uint32_t i = base + threadIdx.x * 4;
+    uint64_t e[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) e[k] = i + k < n ? len[i + k] : 0;
+    const uint64_t v = e[0] + e[1] + e[2] + e[3];
+    uint64_t x = v;
     for (int d = 1; d < 32; d <<= 1) { uint64_t y = __shfl_up_sync(0xFFFFFFFFu, x, d); if (lane >= d) x += y; }
     if (lane == 31) warp_sum[warp] = x;
     __syncthreads();
@@ -132,9 +136,10 @@ __global__ void __launch_bounds__(1024) avr_k_exclusive_scan_u32(const uint32_t*
     }
     __syncthreads();
     uint64_t excl = carry + warp_sum[warp] + x - v;
-    if (i < n) off[i] = excl;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { if (i + k < n) off[i + k] = excl; excl += e[k]; }
     __syncthreads();
-    if (threadIdx.x == 1023) carry = excl + v;
+    if (threadIdx.x == 1023) carry = excl;
     __syncthreads();
   }
   if (threadIdx.x == 0) *total = carry;

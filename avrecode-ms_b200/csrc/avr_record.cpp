@@ -64,7 +64,7 @@ int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(co
     // libavcodec's CABAC reader may look one or two bytes past `size` (a lone 0x80 stop-bit byte
     // is excluded from size but still in its buffer, cabac_functions.h refill): give ours the same view
     loc.payload_avail = rbsp.size() - start;
-    loc.raw_off = nal.start + 1 + map[start];
+    loc.raw_off = nal.start + 1 + rbsp_to_raw(map, start);
     int rc = on_slice(loc);
     if (rc) return rc;
   }

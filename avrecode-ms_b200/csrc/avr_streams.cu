@@ -41,6 +41,11 @@ __global__ void __launch_bounds__(AVR_STREAM_BLOCK) avr_k_stream_decode(const ui
   if (s < nstreams) avr_body_stream_decode<DIGIT_BITS, MODEL>(s, coded, coded_off, nbins, &dt, bits_out);
 }
 
+__global__ void __launch_bounds__(256) avr_k_stream_scratch_off(uint64_t* off, uint32_t n, uint32_t cap) {
+  const uint32_t s = blockIdx.x * 256 + threadIdx.x;
+  if (s < n) off[s] = (uint64_t)s * cap;
+}
+
 #define CU(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { avr_set_error("%s: %s", #x, cudaGetErrorString(e_)); rc = AVR_E_CUDA; goto done; } } while (0)
 
 static int check_args(avr_context* ctx, uint32_t nstreams, uint32_t nbins, int digit_bits, int model) {
@@ -65,7 +70,7 @@ extern "C" int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_
   const uint32_t cap = avr_stream_cap(nbins, model);
   const size_t nbytes = (size_t)nstreams * nbins;
   uint8_t *d_bits = nullptr, *d_scratch = nullptr, *d_out = nullptr;
-  uint32_t* d_len = nullptr; int* d_status = nullptr; uint64_t *d_off = nullptr; AvrDivTab* d_div = nullptr;
+  uint32_t* d_len = nullptr; int* d_status = nullptr; uint64_t *d_off = nullptr, *d_soff = nullptr; AvrDivTab* d_div = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   std::vector<int> status(nstreams);
   std::vector<uint32_t> len(nstreams);
@@ -79,6 +84,7 @@ extern "C" int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_
   CU(cudaMalloc(&d_len, sizeof(uint32_t) * nstreams));
   CU(cudaMalloc(&d_status, sizeof(int) * nstreams));
   CU(cudaMalloc(&d_off, sizeof(uint64_t) * (nstreams + 1)));
+  CU(cudaMalloc(&d_soff, sizeof(uint64_t) * nstreams));
   CU(cudaMalloc(&d_div, sizeof(AvrDivTab)));
   CU(cudaEventRecord(ev[0], st));
   CU(cudaMemcpyAsync(d_div, &h_div, sizeof h_div, cudaMemcpyHostToDevice, st));
@@ -91,17 +97,11 @@ extern "C" int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_
   CU(cudaGetLastError());
   {
     // per-stream scratch -> one contiguous buffer (device-side exclusive scan of the lengths, then a gather)
-    std::vector<uint64_t> soff(nstreams);
-    for (uint32_t s = 0; s < nstreams; s++) soff[s] = (uint64_t)s * cap;
-    uint64_t* d_soff = nullptr;
-    CU(cudaMalloc(&d_soff, sizeof(uint64_t) * nstreams));
-    cudaError_t e1 = cudaMemcpyAsync(d_soff, soff.data(), sizeof(uint64_t) * nstreams, cudaMemcpyHostToDevice, st);
-    int lrc = e1 == cudaSuccess ? avr_launch_compact(d_scratch, d_soff, d_len, d_off, d_off + nstreams, d_out, nstreams, st) : (int)e1;
-    cudaError_t e2 = cudaEventRecord(ev[2], st);
-    cudaError_t e3 = cudaStreamSynchronize(st);
-    cudaFree(d_soff);
-    if (lrc || e2 != cudaSuccess || e3 != cudaSuccess) { avr_set_error("streams: compaction failed (%d)", lrc ? lrc : (int)(e2 ? e2 : e3)); rc = AVR_E_CUDA; goto done; }
+    avr_k_stream_scratch_off<<<(nstreams + 255) / 256, 256, 0, st>>>(d_soff, nstreams, cap);
+    const int lrc = avr_launch_compact(d_scratch, d_soff, d_len, d_off, d_off + nstreams, d_out, nstreams, st);
+    if (lrc) { avr_set_error("streams: compaction failed (%d)", lrc); rc = AVR_E_CUDA; goto done; }
   }
+  CU(cudaEventRecord(ev[2], st));
   CU(cudaMemcpyAsync(coded_off, d_off, sizeof(uint64_t) * (nstreams + 1), cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(status.data(), d_status, sizeof(int) * nstreams, cudaMemcpyDeviceToHost, st));
   CU(cudaMemcpyAsync(len.data(), d_len, sizeof(uint32_t) * nstreams, cudaMemcpyDeviceToHost, st));
@@ -118,12 +118,12 @@ extern "C" int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_
   if (t) {
     t->h2d_ms = ev_ms(ev[0], ev[1]); t->kernel_ms = ev_ms(ev[1], ev[2]); t->d2h_ms = ev_ms(ev[2], ev[3]);
     t->h2d_bytes = nbytes; t->d2h_bytes = total + (uint64_t)nstreams * 16 + 8;
-    t->bins = (uint64_t)nstreams * nbins; t->coded_symbols = t->bins; t->launches = 3;
+    t->bins = (uint64_t)nstreams * nbins; t->coded_symbols = t->bins; t->launches = 4;
     t->coder_launch_ms_x1000 = (uint32_t)(t->kernel_ms * 1000.0);
   }
 done:
   if (rc && coded->data) { free(coded->data); coded->data = nullptr; coded->size = 0; }
-  cudaFree(d_bits); cudaFree(d_scratch); cudaFree(d_out); cudaFree(d_len); cudaFree(d_status); cudaFree(d_off); cudaFree(d_div);
+  cudaFree(d_bits); cudaFree(d_scratch); cudaFree(d_out); cudaFree(d_len); cudaFree(d_status); cudaFree(d_off); cudaFree(d_soff); cudaFree(d_div);
   for (auto& e : ev) if (e) cudaEventDestroy(e);
   return rc;
 }

@@ -282,33 +282,58 @@ struct NalSpan {
 // Finds the next NAL at or after `pos`. NAL end = first "00 00 0x" (x<=2... i.e. 00 00 00 / 00 00 01
 // / 00 00 02) after the header, like ff_h264_decode_nal, else end of buffer.
 static inline bool next_nal(const uint8_t* d, size_t n, size_t pos, NalSpan* out) {
+  // start code: first 00 00 01 at or after pos (memchr for the zero, then two compares)
   size_t i = pos;
-  while (i + 3 <= n && !(d[i] == 0 && d[i + 1] == 0 && d[i + 2] == 1)) i++;
-  if (i + 3 > n) return false;
-  size_t s = i + 3;
+  for (;;) {
+    if (i + 3 > n) return false;
+    const uint8_t* z = static_cast<const uint8_t*>(memchr(d + i, 0, n - 2 - i));
+    if (!z) return false;
+    i = (size_t)(z - d);
+    if (d[i + 1] == 0 && d[i + 2] == 1) break;
+    i++;
+  }
+  const size_t s = i + 3;
   if (s >= n) return false;
+  // end: first 00 00 0x with x <= 2 at e >= s + 1, e + 2 < n; else the end of the buffer
   size_t e = s + 1;
-  while (e + 2 < n) {
-    if (d[e] == 0 && d[e + 1] == 0 && d[e + 2] <= 3 && d[e + 2] != 3) break;
+  for (;;) {
+    if (e + 2 >= n) { e = n; break; }
+    const uint8_t* z = static_cast<const uint8_t*>(memchr(d + e, 0, n - 2 - e));
+    if (!z) { e = n; break; }
+    e = (size_t)(z - d);
+    if (d[e + 1] == 0 && d[e + 2] <= 2) break;
     e++;
   }
-  if (e + 2 >= n) e = n;
   out->start = s; out->end = e;
   return true;
 }
 
-// Unescape NAL payload (after the header byte) into `rbsp`; `map` (optional) gets, for each
-// RBSP byte, its offset in the raw NAL payload.
-static inline void unescape_nal(const uint8_t* p, size_t n, std::vector<uint8_t>* rbsp, std::vector<uint32_t>* map) {
+// Unescape NAL payload (after the header byte) into `rbsp`: every 03 that follows two zero bytes is dropped
+// (ff_h264_decode_nal).  `esc` (optional) gets the RBSP offset at which each dropped byte sat, ascending, so that
+// the raw offset of RBSP byte k is k + (number of entries <= k).  Segments between escapes are copied whole.
+static inline void unescape_nal(const uint8_t* p, size_t n, std::vector<uint8_t>* rbsp, std::vector<uint32_t>* esc) {
   rbsp->clear();
-  if (map) map->clear();
-  int zeros = 0;
-  for (size_t i = 0; i < n; i++) {
-    if (zeros >= 2 && p[i] == 3) { zeros = 0; continue; }  // ff_h264_decode_nal drops every 00 00 03
-    rbsp->push_back(p[i]);
-    if (map) map->push_back((uint32_t)i);
-    zeros = p[i] == 0 ? zeros + 1 : 0;
+  if (esc) esc->clear();
+  rbsp->reserve(n);
+  size_t seg = 0;
+  for (size_t i = 2; i < n;) {
+    const uint8_t* q = static_cast<const uint8_t*>(memchr(p + i, 3, n - i));
+    if (!q) break;
+    i = (size_t)(q - p);
+    if (p[i - 1] == 0 && p[i - 2] == 0 && i - 2 >= seg) {     // both zeros were kept bytes of this segment
+      rbsp->insert(rbsp->end(), p + seg, p + i);
+      if (esc) esc->push_back((uint32_t)rbsp->size());
+      seg = i + 1;
+    }
+    i++;
   }
+  rbsp->insert(rbsp->end(), p + seg, p + n);
+}
+// raw offset (within the NAL payload) of RBSP byte k
+static inline size_t rbsp_to_raw(const std::vector<uint32_t>& esc, size_t k) {
+  size_t lo = 0, hi = esc.size();
+  while (lo < hi) { const size_t mid = (lo + hi) / 2; if (esc[mid] <= k) lo = mid + 1; else hi = mid; }
+  return k + lo;
 }
 
 }  // namespace avr

@@ -257,7 +257,7 @@ def main():
         streams = None
         if rank == 0 and not args.no_single:
             import numpy as np
-            S, N = 8192, 16384
+            S, N = 65536, 2048
             rng = np.random.RandomState(1)
             pr = np.array([0.5, 0.1, 0.01, 0.001])[np.arange(S) % 4][:, None]
             sbits = (rng.random_sample((S, N)) < pr).astype(np.uint8)
