@@ -97,6 +97,26 @@ def test_gpu_streams_large_roundtrip_and_oracle_sample(ctx, digit_bits, model, t
 
 
 @pytest.mark.gpu
+def test_gpu_streams_ragged_batch(ctx, tmpdir_path):
+    """a stream count that is no multiple of the block (128) or of the compaction scan's step (4096) and a bin count that is
+    no multiple of 8: every stream round-trips and first / middle / last streams equal the oracle"""
+    import avr_ctypes as A
+    S, N = 5003, 257
+    rng = np.random.RandomState(9)
+    bits = (rng.random_sample((S, N)) < 0.2).astype(np.uint8)
+    for digit_bits, model in ((16, 0), (8, 1)):
+        coded, _ = A.streams_encode(ctx, bits.tobytes(), S, N, digit_bits, model)
+        back, _ = A.streams_decode(ctx, coded, S, N, digit_bits, model)
+        assert back == bits.tobytes()
+        sample = [0, 127, 128, 4095, 4096, 4097, S - 1]
+        pth = os.path.join(tmpdir_path, "s.bin")
+        open(pth, "wb").write(bits[sample].tobytes())
+        out = subprocess.run([os.path.join(REF, "avr_oracle"), "streams", str(digit_bits), str(model), str(len(sample)), str(N), pth],
+                             stdout=subprocess.PIPE, check=True).stdout
+        assert [coded[s].hex() for s in sample] == [l[2:].strip().decode() for l in out.splitlines() if l.startswith(b"A")]
+
+
+@pytest.mark.gpu
 def test_gpu_streams_bad_arguments(ctx):
     import avr_ctypes as A
     with pytest.raises(A.AvrError):
