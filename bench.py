@@ -154,10 +154,14 @@ def main():
         print(json.dumps(line))
         return
 
+    # stdout carries exactly ONE JSON line: native libraries (NCCL's version banner, for one) write to fd 1 directly,
+    # so fd 1 points at stderr for the whole run and the line goes to the saved descriptor at the end
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import avr_ctypes as A
     if world > 1:
-        # NCCL prints its version banner on stdout when NCCL_DEBUG is set: keep stdout for the one JSON line
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
@@ -351,7 +355,8 @@ def main():
                                         "sample": f"first {nref} clips of the corpus, oracle/_ref/recode roundtrip, one process per core"}
         else:
             line["cpu_baseline"] = {"value": None, "unit": "MB/s", "cores": cores, "kind": "reference", "sample": "oracle/_ref/recode missing"}
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 
