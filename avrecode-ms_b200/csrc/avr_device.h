@@ -65,8 +65,9 @@ struct AvrRangeEnc {
     range <<= 8;
   }
   AVR_HD void put(int symbol, uint64_t range_of_1) {
-    uint64_t range_of_0 = range - range_of_1;
-    if (symbol) { low += range_of_0; range = range_of_1; } else { range = range_of_0; }
+    const uint64_t range_of_0 = range - range_of_1;
+    low += symbol ? range_of_0 : 0ull;                 // selects: lanes that code different slices stay converged
+    range = symbol ? range_of_1 : range_of_0;
     if (range < (1ull << 51)) {
       if (range == 0) { err = AVR_E_CORRUPT; range = 1; }
       while (range < (1ull << 55)) emit_digit();
