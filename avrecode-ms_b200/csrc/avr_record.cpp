@@ -32,6 +32,25 @@ struct RecordIO {
 
 }  // namespace
 
+// The block finder's memmem (recode.cpp:1283-1286): FIRST occurrence of the unescaped payload in the original bytes
+// not yet emitted, here bounded by the end of the slice's own NAL.  A payload without emulation-prevention bytes sits
+// at its raw offset, so that place is compared first (memcmp) and the general search (glibc's two-way memmem, slow
+// on needles of tens of KB) runs only when that fails or when the payload's first 8 bytes also occur earlier in the
+// window, i.e. only when an earlier occurrence is possible at all.
+static bool find_payload(const uint8_t* data, size_t n, size_t prev_coded_end, const SliceLoc& loc, size_t* found_at) {
+  const size_t hay_end = loc.raw_off + loc.size <= n ? loc.raw_off + loc.size : n;
+  if (loc.raw_off + loc.size <= n && memcmp(data + loc.raw_off, loc.payload, loc.size) == 0) {
+    const size_t before = loc.raw_off - prev_coded_end;        // bytes in front of the raw offset
+    const size_t span = before + 7 < hay_end - prev_coded_end ? before + 7 : hay_end - prev_coded_end;
+    const void* m8 = before ? memmem(data + prev_coded_end, span, loc.payload, 8) : nullptr;   // a match must start before raw_off
+    if (!m8) { *found_at = loc.raw_off; return true; }
+  }
+  const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, loc.payload, loc.size);
+  if (!m) return false;
+  *found_at = (size_t)((const uint8_t*)m - data);
+  return true;
+}
+
 int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice) {
   std::vector<Sps> sps(32);
   std::vector<Pps> pps(256);
@@ -81,11 +100,7 @@ int scan_annexb(const uint8_t* data, size_t n, FileRecord* out, std::vector<Scan
     if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);
     bool found = false;
     size_t found_at = 0;
-    if (loc.size >= 8 && loc.raw_off >= prev_coded_end) {
-      size_t hay_end = loc.raw_off + loc.size <= n ? loc.raw_off + loc.size : n;
-      const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, loc.payload, loc.size);
-      if (m) { found = true; found_at = (size_t)((const uint8_t*)m - data); }
-    }
+    if (loc.size >= 8 && loc.raw_off >= prev_coded_end) found = find_payload(data, n, prev_coded_end, loc, &found_at);
     rec.slice_begin(found, found ? found_at : loc.raw_off, (uint32_t)loc.size, sh.sp);
     if (!found) return 0;
     prev_coded_end = found_at + loc.size;
@@ -112,11 +127,7 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
     // recode.cpp:1283-1286: memmem of the unescaped payload in the not-yet-emitted original bytes
     bool found = false;
     size_t found_at = 0;
-    if (loc.size >= 8 && loc.raw_off >= prev_coded_end) {
-      size_t hay_end = loc.raw_off + loc.size <= n ? loc.raw_off + loc.size : n;
-      const void* m = memmem(data + prev_coded_end, hay_end - prev_coded_end, loc.payload, loc.size);
-      if (m) { found = true; found_at = (size_t)((const uint8_t*)m - data); }
-    }
+    if (loc.size >= 8 && loc.raw_off >= prev_coded_end) found = find_payload(data, n, prev_coded_end, loc, &found_at);
     rec.slice_begin(found, found ? found_at : loc.raw_off, (uint32_t)loc.size, sh.sp);
     if (!found) return 0;
     prev_coded_end = found_at + loc.size;

@@ -114,6 +114,7 @@ def main():
     ap.add_argument("--ref-clips", type=int, default=int(os.environ.get("AVR_BENCH_REF_CLIPS", "0")),
                     help="reference sample size (0 = 8 per host core)")
     ap.add_argument("--no-single", action="store_true", help="skip the single-clip (config 2) side measurement")
+    ap.add_argument("--host-threads", type=int, default=0, help="host threads of the e2e calls (0 = host cores / ranks)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -225,7 +226,7 @@ def main():
         # ---- e2e: public file-level API, host buffers ----
         e2e_t = []
         h2d = d2h = 0
-        host_threads = max(2, cores // world)      # the ranks of one box share its host cores
+        host_threads = args.host_threads or max(2, cores // world)      # the ranks of one box share its host cores
         for s in range(2):
             barrier()
             t0 = time.perf_counter()
