@@ -252,27 +252,59 @@ class DBatch:
             self.h = C.c_void_p()
 
 
-def _files_call(fn, ctx, blobs, threads):
+class FileResults:
+    """Library-owned output buffers of avr_compress_files / avr_decompress_files, exposed without a copy (what a C or
+    C++ caller gets): views[i] is a memoryview over file i; close() hands the buffers back (avr_buffer_free)."""
+
+    def __init__(self, outs, n):
+        self._outs, self._n = outs, n
+        self.views = [memoryview((C.c_uint8 * outs[i].size).from_address(C.addressof(outs[i].data.contents))).cast("B")
+                      if outs[i].size else memoryview(b"") for i in range(n)]
+
+    def close(self):
+        self.views = []
+        for i in range(self._n):
+            lib().avr_buffer_free(C.byref(self._outs[i]))
+        self._n = 0
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def _files_call(fn, ctx, blobs, threads, copy=True):
     n = len(blobs)
-    ins = (C.c_char_p * n)(*blobs)
+    ins = (C.c_void_p * n)()
+    keep = []
+    for i, b in enumerate(blobs):            # bytes or any contiguous buffer (e.g. the views of a previous call)
+        if isinstance(b, bytes):
+            ins[i] = C.cast(C.c_char_p(b), C.c_void_p)
+        else:
+            arr = (C.c_uint8 * len(b)).from_buffer(b) if not b.readonly else (C.c_uint8 * len(b)).from_buffer_copy(b)
+            keep.append(arr)
+            ins[i] = C.addressof(arr)
     lens = (C.c_size_t * n)(*[len(b) for b in blobs])
     outs = (Buffer * n)()
     t = Timing()
-    _check(fn(ctx.h, ins, lens, n, threads, outs, C.byref(t)))
+    _check(fn(ctx.h, C.cast(ins, C.POINTER(C.c_char_p)), lens, n, threads, outs, C.byref(t)))
+    if not copy:
+        return FileResults(outs, n), t.as_dict()
     res = [C.string_at(outs[i].data, outs[i].size) for i in range(n)]
     for i in range(n):
         lib().avr_buffer_free(C.byref(outs[i]))
     return res, t.as_dict()
 
 
-def compress_files(ctx, blobs, threads=0):
-    """`recode compress` for a batch of Annex-B H.264 byte strings -> .avrec byte strings."""
-    return _files_call(lib().avr_compress_files, ctx, blobs, threads or (os.cpu_count() or 1))
+def compress_files(ctx, blobs, threads=0, copy=True):
+    """`recode compress` for a batch of Annex-B H.264 byte strings -> .avrec byte strings (copy=False: FileResults)."""
+    return _files_call(lib().avr_compress_files, ctx, blobs, threads or (os.cpu_count() or 1), copy)
 
 
-def decompress_files(ctx, blobs, threads=0):
-    """`recode decompress` for a batch of .avrec byte strings -> original byte strings."""
-    return _files_call(lib().avr_decompress_files, ctx, blobs, threads or (os.cpu_count() or 1))
+def decompress_files(ctx, blobs, threads=0, copy=True):
+    """`recode decompress` for a batch of .avrec byte strings -> original byte strings (copy=False: FileResults)."""
+    return _files_call(lib().avr_decompress_files, ctx, blobs, threads or (os.cpu_count() or 1), copy)
 
 
 def streams_encode(ctx, bits, nstreams, nbins, digit_bits=16, model=STREAM_FIXED_HALF):
