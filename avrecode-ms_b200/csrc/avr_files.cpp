@@ -363,8 +363,48 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
     if (files[f].rc) { avr_set_error("container %d: invalid (%d)", f, files[f].rc); return files[f].rc; }
 
   avr_trace("d: containers+scan");
-  std::vector<std::vector<std::vector<uint8_t>>> decoded((size_t)n);   // [file][slice] bytes after the padding patch
-  for (int f = 0; f < n; f++) decoded[f].resize(files[f].slices.size());
+  // Output files are assembled straight from the batch's device-fetched slice bytes (one copy per byte): literal
+  // blocks from the container, coded blocks from the batch with the x264 padding patch applied in place
+  // (recode.cpp:1352-1362, 1387-1391: the last byte is replaced, or appended when the length parity differs).
+  std::atomic<int> nomem(0);
+  auto patched_len = [](const Block& blk, uint32_t len) -> size_t {
+    if (blk.has_parity && blk.has_last && blk.last_len > 0 && blk.parity != (int)(len & 1)) return (size_t)len + 1;
+    return len;
+  };
+  auto assemble = [&](int f, const avr_dbatch* b, uint32_t first_slice) {
+    DFile& d = files[f];
+    std::vector<int> blk_slice(d.blocks.size(), -1);
+    for (size_t k = 0; k < d.slice_block.size(); k++) blk_slice[d.slice_block[k]] = (int)k;
+    size_t total = 0;
+    for (size_t i = 0; i < d.blocks.size(); i++) {
+      const Block& blk = d.blocks[i];
+      if (blk.has_literal) total += blk.literal_len;
+      else if (blk.has_cabac) {
+        const uint8_t* p; uint32_t len;
+        avr_dbatch_slice(b, first_slice + (uint32_t)blk_slice[i], &p, &len, nullptr);
+        total += patched_len(blk, len);
+      }
+    }
+    out[f].size = total;
+    out[f].data = (uint8_t*)malloc(total ? total : 1);
+    if (!out[f].data) { nomem = 1; return; }
+    uint8_t* o = out[f].data;
+    for (size_t i = 0; i < d.blocks.size(); i++) {
+      const Block& blk = d.blocks[i];
+      if (blk.has_literal) { if (blk.literal_len) memcpy(o, blk.literal, blk.literal_len); o += blk.literal_len; }
+      else if (blk.has_cabac) {
+        const uint8_t* p; uint32_t len;
+        avr_dbatch_slice(b, first_slice + (uint32_t)blk_slice[i], &p, &len, nullptr);
+        if (len) memcpy(o, p, len);
+        if (blk.has_parity && blk.has_last && blk.last_len > 0) {
+          if (blk.parity != (int)(len & 1)) o[len] = blk.last[0];
+          else if (len) o[len - 1] = blk.last[0];
+        }
+        o += patched_len(blk, len);
+      }
+    }
+  };
+  std::vector<char> assembled((size_t)n, 0);
   int rc = AVR_OK;
   int f0 = 0;
   while (f0 < n && rc == AVR_OK) {
@@ -392,47 +432,14 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
       avr_timing t; avr_dbatch_timing(b, &t); add_timing(&tt, t);
       std::vector<uint32_t> first(ids.size(), 0);
       for (size_t k = 1; k < ids.size(); k++) first[k] = first[k - 1] + per[k - 1];
-      parallel_for((int)ids.size(), host_threads, [&](int k) {
-        DFile& d = files[ids[k]];
-        uint32_t g = first[k];
-        for (size_t s = 0; s < d.slices.size(); s++, g++) {
-          const uint8_t* p; uint32_t len;
-          avr_dbatch_slice(b, g, &p, &len, nullptr);
-          std::vector<uint8_t>& o = decoded[ids[k]][s];
-          o.assign(p, p + len);
-          const Block& blk = d.blocks[d.slice_block[s]];
-          if (blk.has_parity && blk.has_last && blk.last_len > 0) {      // x264 padding patch, recode.cpp:1352-1362, 1387-1391
-            if (blk.parity != (int)(o.size() & 1)) o.push_back(blk.last[0]);
-            else if (!o.empty()) o.back() = blk.last[0];
-          }
-        }
-      });
-      avr_trace("d: patch copies");
+      parallel_for((int)ids.size(), host_threads, [&](int k) { assemble(ids[k], b, first[k]); assembled[ids[k]] = 1; });
+      avr_trace("d: assemble batch");
     }
     avr_dbatch_destroy(b);
     avr_trace("d: destroy");
   }
-  if (rc != AVR_OK) return rc;
-  std::atomic<int> nomem(0);
-  parallel_for(n, host_threads, [&](int f) {
-    DFile& d = files[f];
-    std::vector<int> blk_slice(d.blocks.size(), -1);
-    for (size_t k = 0; k < d.slice_block.size(); k++) blk_slice[d.slice_block[k]] = (int)k;
-    size_t total = 0;
-    for (size_t i = 0; i < d.blocks.size(); i++) {
-      const Block& b = d.blocks[i];
-      total += b.has_literal ? b.literal_len : b.has_cabac ? decoded[f][blk_slice[i]].size() : 0;
-    }
-    out[f].size = total;
-    out[f].data = (uint8_t*)malloc(total ? total : 1);
-    if (!out[f].data) { nomem = 1; return; }
-    uint8_t* o = out[f].data;
-    for (size_t i = 0; i < d.blocks.size(); i++) {
-      const Block& b = d.blocks[i];
-      if (b.has_literal) { if (b.literal_len) memcpy(o, b.literal, b.literal_len); o += b.literal_len; }
-      else if (b.has_cabac) { const auto& v = decoded[f][blk_slice[i]]; if (!v.empty()) memcpy(o, v.data(), v.size()); o += v.size(); }
-    }
-  });
+  if (rc != AVR_OK) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return rc; }
+  parallel_for(n, host_threads, [&](int f) { if (!assembled[f]) assemble(f, nullptr, 0); });   // files without coded blocks: literals only
   if (nomem) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return AVR_E_NOMEM; }
   avr_trace("d: assemble");
   tt.host_ms = now_ms() - t_call0 - (tt.h2d_ms + tt.kernel_ms + tt.d2h_ms);
