@@ -15,25 +15,45 @@
 
 namespace {
 
+// A container under construction: malloc-backed so that the finished bytes become the caller's avr_buffer without a copy.
+struct Buf {
+  uint8_t* p = nullptr; size_t n = 0, cap = 0; bool bad = false;
+  Buf() = default;
+  Buf(const Buf&) = delete; Buf& operator=(const Buf&) = delete;
+  Buf(Buf&& o) noexcept : p(o.p), n(o.n), cap(o.cap), bad(o.bad) { o.p = nullptr; o.n = o.cap = 0; }
+  ~Buf() { free(p); }
+  void reserve(size_t c) {
+    if (c <= cap) return;
+    uint8_t* q = (uint8_t*)realloc(p, c);
+    if (!q) { bad = true; return; }
+    p = q; cap = c;
+  }
+  bool room(size_t k) { if (n + k > cap) reserve((n + k) + (n + k) / 2 + 64); return n + k <= cap; }
+  void push_back(uint8_t v) { if (room(1)) p[n++] = v; }
+  void append(const uint8_t* s, size_t k) { if (k && room(k)) { memcpy(p + n, s, k); n += k; } }
+  void clear() { n = 0; }
+  size_t size() const { return n; }
+};
+
 // ---- proto2 wire writer (fields in tag order, set-but-empty fields are emitted) ----------------
-void put_varint(std::vector<uint8_t>& o, uint64_t v) {
+void put_varint(Buf& o, uint64_t v) {
   while (v >= 0x80) { o.push_back((uint8_t)(v | 0x80)); v >>= 7; }
   o.push_back((uint8_t)v);
 }
 size_t varint_len(uint64_t v) { size_t n = 1; while (v >= 0x80) { v >>= 7; n++; } return n; }
-void put_bytes_field(std::vector<uint8_t>& o, uint8_t tag, const uint8_t* p, size_t n) {
-  o.push_back(tag); put_varint(o, n); o.insert(o.end(), p, p + n);
+void put_bytes_field(Buf& o, uint8_t tag, const uint8_t* p, size_t n) {
+  o.push_back(tag); put_varint(o, n); o.append(p, n);
 }
-void put_block_literal(std::vector<uint8_t>& o, const uint8_t* p, size_t n) {
+void put_block_literal(Buf& o, const uint8_t* p, size_t n) {
   o.push_back(0x12); put_varint(o, 1 + varint_len(n) + n);
   put_bytes_field(o, 0x12, p, n);
 }
-void put_block_skip(std::vector<uint8_t>& o, uint64_t size) {
+void put_block_skip(Buf& o, uint64_t size) {
   o.push_back(0x12); put_varint(o, 1 + varint_len(size) + 2);
   o.push_back(0x08); put_varint(o, size);
   o.push_back(0x18); o.push_back(0x01);
 }
-void put_block_cabac(std::vector<uint8_t>& o, uint64_t size, const uint8_t* cabac, size_t n, int parity, const uint8_t* last_byte) {
+void put_block_cabac(Buf& o, uint64_t size, const uint8_t* cabac, size_t n, int parity, const uint8_t* last_byte) {
   size_t body = 1 + varint_len(size) + 1 + varint_len(n) + n + 2 + (last_byte ? 3 : 0);
   o.push_back(0x12); put_varint(o, body);
   o.push_back(0x08); put_varint(o, size);
@@ -129,11 +149,11 @@ void avr_trace(const char* what) {
 namespace {
 double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
-bool to_buffer(const std::vector<uint8_t>& v, avr_buffer* b) {
-  b->size = v.size();
-  b->data = (uint8_t*)malloc(v.size() ? v.size() : 1);
-  if (!b->data) return false;
-  if (!v.empty()) memcpy(b->data, v.data(), v.size());
+bool to_buffer(Buf& v, avr_buffer* b) {          // hands the bytes over: no copy
+  if (v.bad) return false;
+  if (!v.p) { v.reserve(1); if (v.bad) return false; }
+  b->size = v.n; b->data = v.p;
+  v.p = nullptr; v.n = v.cap = 0;
   return true;
 }
 
@@ -145,7 +165,7 @@ extern "C" void avr_buffer_free(avr_buffer* b) { if (b) { free(b->data); b->data
 // Phase 1 of avr_compress_files: batches whose CABAC parse runs on the GPU (avr_cbatch_create_files).
 // Marks done[f] for every file it produced a container for; the rest fall to the host recorder.
 static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, const std::vector<int>& ids,
-                                 int host_threads, std::vector<std::vector<uint8_t>>& containers, std::vector<char>& done,
+                                 int host_threads, std::vector<Buf>& containers, std::vector<char>& done,
                                  avr_timing* tt) {
   if (ids.empty()) return AVR_OK;
   std::vector<const uint8_t*> fin; std::vector<size_t> flen;
@@ -170,7 +190,7 @@ static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, con
     parallel_for((int)ids.size(), host_threads, [&](int k) {
       if (status[k]) return;
       const int f = ids[k];
-      std::vector<uint8_t>& o = containers[f];
+      Buf& o = containers[f];
       o.reserve(in_len[f] + in_len[f] / 16 + 64);
       uint32_t nspans = 0; avr_cbatch_span_count(b, k, &nspans);
       size_t prev_end = 0;
@@ -200,7 +220,7 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
   if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
   avr_timing tt; memset(&tt, 0, sizeof tt);
   const double t_call0 = now_ms();
-  std::vector<std::vector<uint8_t>> containers((size_t)n);
+  std::vector<Buf> containers((size_t)n);
   std::vector<char> done((size_t)n, 0);
   int rc = AVR_OK;
   // AVR_HOST_PARSE=1 keeps the CABAC parse on the host cores (A/B measurement, bench.py)
@@ -255,7 +275,7 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
       parallel_for((int)files.size(), host_threads, [&](int k) {
         const int f = files[k];
         const avr::FileRecord& r = *avr_record_view(recs[f]);
-        std::vector<uint8_t>& o = containers[f];
+        Buf& o = containers[f];
         o.reserve(in_len[f] + in_len[f] / 16 + 64);
         size_t prev_end = 0;
         for (const avr::SliceSpan& sp : r.spans) {
