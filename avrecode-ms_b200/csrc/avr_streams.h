@@ -28,13 +28,46 @@ struct AvrStreamEnc {
   uint8_t* out;
   uint32_t n, cap;
   int err;
-  AVR_HD void init(uint8_t* o, uint32_t c) { low = 0; range = 1ull << 63; out = o; n = 0; cap = c; err = 0; }
-  AVR_HD void push(uint32_t b) { if (n < cap) out[n] = (uint8_t)b; else err = AVR_E_OVERFLOW; n++; }
-  // the reference parks digits a later carry could still change in `overflow` (arithmetic_code.h:153-174); here they
-  // are written at once and the carry walks back through them: same bytes
+  // Output bytes wait in registers and leave eight at a time as one aligned store: `acc` collects the newest bytes
+  // (oldest on top), `held` is the last complete group, written only when the next one is complete.  A carry
+  // (arithmetic_code.h:153-159) then ends in registers unless eight or more pending bytes are all 0xFF; without the
+  // held group every carry right after a store was a read-modify-write of global memory on the coder's critical path
+  // (about every other 16-bit digit of an incompressible stream).  n counts all bytes pushed; the scratch of a stream
+  // starts 16-byte aligned.
+  uint64_t acc, held;
+  AVR_HD void init(uint8_t* o, uint32_t c) { low = 0; range = 1ull << 63; out = o; n = 0; cap = c; err = 0; acc = 0; held = 0; }
+  AVR_HD void store_group(uint32_t at, uint64_t w) {             // eight bytes, oldest first, at byte offset `at`
+    if (at + 8 > cap) { err = AVR_E_OVERFLOW; return; }
+    w = ((w & 0x00FF00FF00FF00FFull) << 8) | ((w >> 8) & 0x00FF00FF00FF00FFull);
+    w = ((w & 0x0000FFFF0000FFFFull) << 16) | ((w >> 16) & 0x0000FFFF0000FFFFull);
+    w = (w << 32) | (w >> 32);
+    *reinterpret_cast<uint64_t*>(out + at) = w;
+  }
+  AVR_HD void push(uint32_t b) {
+    acc = (acc << 8) | (uint64_t)(b & 0xFF);
+    n++;
+    if ((n & 7) == 0) {
+      if (n >= 16) store_group(n - 16, held);
+      held = acc; acc = 0;
+    }
+  }
   AVR_HD void carry_back() {
-    uint32_t i = n < cap ? n : cap;
+    const uint32_t pend = n & 7;
+    if (pend) {
+      acc += 1;
+      if ((acc >> (8 * pend)) == 0) return;
+      acc &= (1ull << (8 * pend)) - 1;                           // all pending bytes were 0xFF
+    }
+    if (n >= 8) { if (++held != 0) return; }                     // the held group; all 0xFF again: on into memory
+    uint32_t i = n >= 8 ? (n & ~7u) - 8 : 0; if (i > cap) i = cap & ~7u;
     while (i > 0) { if (++out[--i] != 0) break; }
+  }
+  AVR_HD void flush() {                                          // after finish(): the held group, then the bytes still in acc
+    const uint32_t pend = n & 7, base = n - pend;
+    if (n >= 8) store_group(base - 8, held);
+    for (uint32_t k = 0; k < pend; k++) {
+      if (base + k < cap) out[base + k] = (uint8_t)(acc >> (8 * (pend - 1 - k))); else err = AVR_E_OVERFLOW;
+    }
   }
   AVR_HD void emit_put_digit() {
     if (low >> 63) { carry_back(); low &= (1ull << 63) - 1; }
@@ -46,7 +79,8 @@ struct AvrStreamEnc {
   }
   AVR_HD void put(int symbol, uint64_t range_of_1) {            // arithmetic_code.h:106-126
     const uint64_t range_of_0 = range - range_of_1;
-    if (symbol) { low += range_of_0; range = range_of_1; } else { range = range_of_0; }
+    low += symbol ? range_of_0 : 0ull;                          // selects: the lanes of a warp code different symbols
+    range = symbol ? range_of_1 : range_of_0;
     if (range < kMinRange) {
       if (range == 0) { err = AVR_E_CORRUPT; range = 1; }       // "emitted a zero-probability symbol"
       while (range < (1ull << kTop)) emit_put_digit();
@@ -63,6 +97,7 @@ struct AvrStreamEnc {
       low = (low & ((1ull << 55) - 1)) << 8;
     }
     range = 0;
+    flush();
   }
 };
 
@@ -96,7 +131,8 @@ struct AvrStreamDec {
   AVR_HD int get(uint64_t range_of_1) {                         // arithmetic_code.h:232-248
     const uint64_t range_of_0 = range - range_of_1;
     const int symbol = low >= range_of_0;
-    if (symbol) { low -= range_of_0; range = range_of_1; } else { range = range_of_0; }
+    low -= symbol ? range_of_0 : 0ull;
+    range = symbol ? range_of_1 : range_of_0;
     if (range < kMinRange) {
       if (range == 0) return symbol;                            // corrupt input: the caller's loop is bounded by nbins
       while (range < (1ull << kTop)) consume();

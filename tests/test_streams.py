@@ -37,6 +37,12 @@ def test_stream_bodies_match_reference_golden(c, tmpdir_path):
     assert tool_streams(os.path.join(ROOT, "build", "avr_emul"), c, tmpdir_path) == c["coded"]
 
 
+@pytest.mark.parametrize("c", CASES[::3], ids=IDS[::3])
+def test_stream_bodies_under_asan(c, tmpdir_path):
+    """same bodies in the ASan/UBSan build of the scaffold: no access outside the per-stream scratch, inputs or outputs"""
+    assert tool_streams(os.path.join(ROOT, "build", "avr_emul_asan"), c, tmpdir_path) == c["coded"]
+
+
 @pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
 def test_oracle_streams_match_live_reference(tmpdir_path):
     rng = np.random.RandomState(77)
