@@ -88,13 +88,19 @@ extern "C" int avr_context_create(int device, avr_context** out) {
   if (prop.major < 10) { avr_set_error("device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major, prop.minor); return AVR_E_CUDA; }
   CU(cudaSetDevice(device));
   avr_context* c = new avr_context();
-  c->device = device;
-  CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  for (auto& e : c->ev) CU(cudaEventCreate(&e));
+  c->device = device; c->stream = nullptr; c->d_tab = nullptr;
+  for (auto& e : c->ev) e = nullptr;
   AvrTables t;
   avr_fill_tables(&t);
-  CU(cudaMalloc(&c->d_tab, sizeof t));
-  CU(cudaMemcpy(c->d_tab, &t, sizeof t, cudaMemcpyHostToDevice));
+  cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  for (auto& ev : c->ev) if (e == cudaSuccess) e = cudaEventCreate(&ev);
+  if (e == cudaSuccess) e = cudaMalloc(&c->d_tab, sizeof t);
+  if (e == cudaSuccess) e = cudaMemcpy(c->d_tab, &t, sizeof t, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {                                  // nothing half-built is left behind
+    avr_set_error("context on device %d: %s", device, cudaGetErrorString(e));
+    avr_context_destroy(c);
+    return AVR_E_CUDA;
+  }
   *out = c;
   return AVR_OK;
 }
@@ -102,12 +108,13 @@ extern "C" void avr_context_destroy(avr_context* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   c->arena.flush(); c->pinned.flush();
-  cudaFree(c->d_tab);
-  for (auto& e : c->ev) cudaEventDestroy(e);
-  cudaStreamDestroy(c->stream);
+  if (c->d_tab) cudaFree(c->d_tab);
+  for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+  if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
 extern "C" void* avr_context_stream(avr_context* c) { return c ? (void*)c->stream : nullptr; }
+int avr_context_device(const avr_context* c) { return c ? c->device : -1; }
 
 // ---- recorder bindings ------------------------------------------------------------------------
 struct avr_record {
@@ -723,7 +730,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
     if (bf->scans[f].rc) continue;                      // never entered the pools
     const uint32_t s0 = s; s += (uint32_t)sc.coded.size();
     if (file_status[f]) continue;
-    fd.bin_off = ps[s0 < ns ? s0 : 0].bin_off; fd.slice_off = (uint32_t)bsl.size(); fd.nslices = (uint32_t)sc.coded.size();
+    fd.bin_off = s0 < ns ? ps[s0].bin_off : 0; fd.slice_off = (uint32_t)bsl.size(); fd.nslices = (uint32_t)sc.coded.size();
     fd.frame_off = (uint32_t)frames.size(); fd.nframes = (uint32_t)sc.rec.frames.size(); fd.block_off = (uint32_t)nblocks;
     fd.pic_mb_base = (uint32_t)pic_mbs;
     for (auto& fr : sc.rec.frames) { uint32_t mm = (uint32_t)fr.mb_w * fr.mb_h; if (mm > fd.max_mbs) fd.max_mbs = mm; pic_mbs += mm; }

@@ -9,3 +9,5 @@ avr::FileRecord* avr_record_mut(avr_record* r);
 uint32_t avr_span_flip(const avr::FileRecord& rec, uint32_t span_index);
 // AVR_TRACE=1: stage wall times on stderr (diagnostics for the e2e path; off by default)
 void avr_trace(const char* what);
+struct avr_context;
+int avr_context_device(const avr_context* ctx);   // CUDA device ordinal of the context

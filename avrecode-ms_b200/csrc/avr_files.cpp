@@ -218,6 +218,7 @@ static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, con
 extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
                                   avr_buffer* out, avr_timing* tacc) {
   if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
+  if (n) memset(out, 0, (size_t)n * sizeof *out);          // output-only: all-null on every failure path
   avr_timing tt; memset(&tt, 0, sizeof tt);
   const double t_call0 = now_ms();
   std::vector<Buf> containers((size_t)n);
@@ -322,6 +323,7 @@ struct DFile {
 extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
                                     avr_buffer* out, avr_timing* tacc) {
   if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
+  if (n) memset(out, 0, (size_t)n * sizeof *out);          // output-only: all-null on every failure path
   avr_timing tt; memset(&tt, 0, sizeof tt);
   const double t_call0 = now_ms();
   avr_trace(nullptr);

@@ -66,6 +66,7 @@ extern "C" int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_
   coded->data = nullptr; coded->size = 0;
   if (t) memset(t, 0, sizeof *t);
   if (nstreams == 0) { coded_off[0] = 0; return AVR_OK; }
+  if (cudaSetDevice(avr_context_device(ctx)) != cudaSuccess) { avr_set_error("streams: cudaSetDevice failed"); return AVR_E_CUDA; }
   cudaStream_t st = (cudaStream_t)avr_context_stream(ctx);
   const uint32_t cap = avr_stream_cap(nbins, model);
   const size_t nbytes = (size_t)nstreams * nbins;
@@ -139,6 +140,7 @@ extern "C" int avr_streams_decode(avr_context* ctx, const uint8_t* coded, const 
     if (coded_off[s + 1] < coded_off[s] || coded_off[s + 1] - coded_off[s] > 0xFFFFFFFFull) { avr_set_error("streams: offsets not ascending at %u", s); return AVR_E_ARG; }
   const uint64_t total = coded_off[nstreams];
   if (total && !coded) { avr_set_error("streams: null argument"); return AVR_E_ARG; }
+  if (cudaSetDevice(avr_context_device(ctx)) != cudaSuccess) { avr_set_error("streams: cudaSetDevice failed"); return AVR_E_CUDA; }
   cudaStream_t st = (cudaStream_t)avr_context_stream(ctx);
   const size_t nbytes = (size_t)nstreams * nbins;
   uint8_t *d_coded = nullptr, *d_bits = nullptr; uint64_t* d_off = nullptr; AvrDivTab* d_div = nullptr;

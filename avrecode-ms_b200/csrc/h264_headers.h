@@ -79,6 +79,13 @@ static inline void skip_scaling_list(BitReader& br, int size) {
   }
 }
 
+static inline uint32_t br_ue_after_scp(BitReader& br, uint32_t chroma_format_idc, int* separate_colour_plane) {
+  if (chroma_format_idc == 3) *separate_colour_plane = (int)br.u(1);
+  return br.ue();                               // bit_depth_luma_minus8
+}
+// Picture sizes the chain kernels accept (avr_dbatch_create enforces the same bound): larger streams are marked
+// unsupported and stored as literal blocks instead of sizing device stores from attacker-chosen values.
+enum { AVR_MAX_MB_DIM = 1024 };
 // rbsp points AFTER the one-byte NAL header
 static inline bool parse_sps(const uint8_t* rbsp, size_t n, Sps* out, int* id_out) {
   BitReader br(rbsp, n * 8);
@@ -86,15 +93,16 @@ static inline bool parse_sps(const uint8_t* rbsp, size_t n, Sps* out, int* id_ou
   s.profile_idc = br.u(8);
   br.u(8);  // constraint flags + reserved
   br.u(8);  // level_idc
-  int id = br.ue();
-  if (id > 31) return false;
+  const uint32_t id = br.ue();                 // unsigned: a 32-bit Exp-Golomb value must not turn into a negative index
+  if (id > 31u) return false;
   int p = s.profile_idc;
   if (p == 100 || p == 110 || p == 122 || p == 244 || p == 44 || p == 83 || p == 86 || p == 118 || p == 128 ||
       p == 138 || p == 139 || p == 134 || p == 135) {
-    s.chroma_format_idc = br.ue();
-    if (s.chroma_format_idc == 3) s.separate_colour_plane = br.u(1);
-    s.bit_depth_luma = 8 + br.ue();
-    s.bit_depth_chroma = 8 + br.ue();
+    const uint32_t cfi = br.ue(), bdl = br_ue_after_scp(br, cfi, &s.separate_colour_plane), bdc = br.ue();
+    if (cfi > 3u || bdl > 6u || bdc > 6u) return false;
+    s.chroma_format_idc = (int)cfi;
+    s.bit_depth_luma = 8 + (int)bdl;
+    s.bit_depth_chroma = 8 + (int)bdc;
     br.u(1);  // qpprime_y_zero_transform_bypass
     if (br.u(1)) {  // seq_scaling_matrix_present
       int cnt = s.chroma_format_idc != 3 ? 8 : 12;
@@ -102,26 +110,34 @@ static inline bool parse_sps(const uint8_t* rbsp, size_t n, Sps* out, int* id_ou
         if (br.u(1)) skip_scaling_list(br, i < 6 ? 16 : 64);
     }
   }
-  s.log2_max_frame_num = 4 + br.ue();
-  s.poc_type = br.ue();
-  if (s.poc_type == 0) s.log2_max_poc_lsb = 4 + br.ue();
-  else if (s.poc_type == 1) {
+  const uint32_t l2fn = br.ue(), poc = br.ue();
+  if (l2fn > 12u || poc > 2u) return false;       // 7.4.2.1.1 ranges; u(log2_max_frame_num) reads at most 16 bits
+  s.log2_max_frame_num = 4 + (int)l2fn;
+  s.poc_type = (int)poc;
+  if (s.poc_type == 0) {
+    const uint32_t l2poc = br.ue();
+    if (l2poc > 12u) return false;
+    s.log2_max_poc_lsb = 4 + (int)l2poc;
+  } else if (s.poc_type == 1) {
     s.delta_pic_order_always_zero = br.u(1);
     br.se(); br.se();
-    int k = br.ue();
-    for (int i = 0; i < k && !br.err(); i++) br.se();
+    const uint32_t k = br.ue();
+    if (k > 255u) return false;
+    for (uint32_t i = 0; i < k && !br.err(); i++) br.se();
   }
   br.ue();  // max_num_ref_frames
   br.u(1);  // gaps_in_frame_num_value_allowed
-  s.mb_w = br.ue() + 1;
-  s.map_h = br.ue() + 1;
+  const uint32_t wm1 = br.ue(), hm1 = br.ue();
+  if (wm1 >= 65535u || hm1 >= 65535u) return false;   // keeps every later product inside 32 bits; > AVR_MAX_MB_DIM goes literal
+  s.mb_w = (int)wm1 + 1;
+  s.map_h = (int)hm1 + 1;
   s.frame_mbs_only = br.u(1);
   if (!s.frame_mbs_only) s.mb_aff = br.u(1);
   s.direct_8x8_inference = br.u(1);
   // frame cropping / VUI not needed
   if (br.err()) return false;
   s.valid = true;
-  *out = s; *id_out = id;
+  *out = s; *id_out = (int)id;
   return true;
 }
 
@@ -138,16 +154,21 @@ static inline bool more_rbsp_data(const uint8_t* rbsp, size_t n, size_t bitpos) 
 static inline bool parse_pps(const uint8_t* rbsp, size_t n, const Sps* sps_tab, Pps* out, int* id_out) {
   BitReader br(rbsp, n * 8);
   Pps p;
-  int id = br.ue();
-  if (id > 255) return false;
-  p.sps_id = br.ue();
-  if (p.sps_id > 31) return false;
+  const uint32_t id = br.ue();
+  if (id > 255u) return false;
+  const uint32_t sid = br.ue();
+  if (sid > 31u) return false;
+  p.sps_id = (int)sid;
   p.cabac = br.u(1);
   p.pic_order_present = br.u(1);
-  p.num_slice_groups = br.ue() + 1;
-  if (p.num_slice_groups > 1) { p.valid = true; *out = p; *id_out = id; return !br.err(); }  // FMO: unsupported, flagged later
-  p.num_ref_default[0] = br.ue() + 1;
-  p.num_ref_default[1] = br.ue() + 1;
+  const uint32_t nsg = br.ue();
+  if (nsg > 7u) return false;
+  p.num_slice_groups = (int)nsg + 1;
+  if (p.num_slice_groups > 1) { p.valid = true; *out = p; *id_out = (int)id; return !br.err(); }  // FMO: unsupported, flagged later
+  const uint32_t nr0 = br.ue(), nr1 = br.ue();
+  if (nr0 > 31u || nr1 > 31u) return false;
+  p.num_ref_default[0] = (int)nr0 + 1;
+  p.num_ref_default[1] = (int)nr1 + 1;
   p.weighted_pred = br.u(1);
   p.weighted_bipred_idc = br.u(2);
   p.pic_init_qp = 26 + br.se();
@@ -168,7 +189,7 @@ static inline bool parse_pps(const uint8_t* rbsp, size_t n, const Sps* sps_tab, 
   }
   if (br.err()) return false;
   p.valid = true;
-  *out = p; *id_out = id;
+  *out = p; *id_out = (int)id;
   return true;
 }
 
@@ -178,12 +199,14 @@ static inline bool parse_slice_header(const uint8_t* rbsp, size_t nbits, int nal
   BitReader br(rbsp, nbits);
   SliceHeaderInfo h;
   h.nal_unit_type = nal_unit_type; h.nal_ref_idc = nal_ref_idc;
-  int first_mb = br.ue();
-  int st = br.ue();
-  if (st > 9) return false;
-  st %= 5;  // 0 P, 1 B, 2 I, 3 SP, 4 SI
-  int pps_id = br.ue();
-  if (br.err() || pps_id > 255 || !pps_tab[pps_id].valid) return false;
+  const uint32_t first_mb_u = br.ue();
+  const uint32_t st_u = br.ue();
+  if (st_u > 9u || first_mb_u > 0x7FFFFFFFu) return false;
+  const int first_mb = (int)first_mb_u;
+  const int st = (int)(st_u % 5u);  // 0 P, 1 B, 2 I, 3 SP, 4 SI
+  const uint32_t pps_id_u = br.ue();
+  if (br.err() || pps_id_u > 255u || !pps_tab[pps_id_u].valid) return false;
+  const int pps_id = (int)pps_id_u;
   const Pps& pps = pps_tab[pps_id];
   if (!sps_tab[pps.sps_id].valid) return false;
   const Sps& sps = sps_tab[pps.sps_id];
@@ -209,8 +232,10 @@ static inline bool parse_slice_header(const uint8_t* rbsp, size_t nbits, int nal
   int num_ref[2] = {pps.num_ref_default[0], pps.num_ref_default[1]};
   if (st == 0 || st == 1 || st == 3) {
     if (br.u(1)) {
-      num_ref[0] = br.ue() + 1;
-      if (st == 1) num_ref[1] = br.ue() + 1;
+      const uint32_t n0 = br.ue();
+      if (n0 > 31u) return false;
+      num_ref[0] = (int)n0 + 1;
+      if (st == 1) { const uint32_t n1 = br.ue(); if (n1 > 31u) return false; num_ref[1] = (int)n1 + 1; }
     }
   }
   if (st != 2 && st != 4) {  // ref_pic_list_modification
@@ -247,28 +272,29 @@ static inline bool parse_slice_header(const uint8_t* rbsp, size_t nbits, int nal
       }
     }
   }
-  int cabac_init_idc = 0;
+  uint32_t cabac_init_idc = 0;
   if (pps.cabac && st != 2 && st != 4) cabac_init_idc = br.ue();
   int qp = pps.pic_init_qp + br.se();
   if (st == 3 || st == 4) { if (st == 3) br.u(1); br.se(); }
   if (pps.deblocking_control) {
     if (br.ue() != 1) { br.se(); br.se(); }
   }
-  if (br.err() || cabac_init_idc > 2) return false;
+  if (br.err() || cabac_init_idc > 2u || qp < -64 || qp > 128) return false;
   h.header_bits = br.pos();
   h.sp.slice_type = st;
   h.sp.first_mb = first_mb;
   h.sp.mb_w = sps.mb_w;
   h.sp.mb_h = sps.map_h * (2 - sps.frame_mbs_only);
   h.sp.num_ref[0] = num_ref[0]; h.sp.num_ref[1] = num_ref[1];
-  h.sp.cabac_init_idc = cabac_init_idc;
+  h.sp.cabac_init_idc = (int)cabac_init_idc;
   h.sp.slice_qp = qp;
   h.sp.transform_8x8_mode = pps.transform_8x8_mode;
   h.sp.chroma_format_idc = sps.chroma_format_idc;
   h.sp.direct_8x8_inference = sps.direct_8x8_inference;
   h.supported = (st == 0 || st == 2) && !field_pic && !sps.mb_aff && sps.frame_mbs_only &&
                 pps.num_slice_groups == 1 && sps.chroma_format_idc <= 1 && sps.bit_depth_luma == 8 &&
-                sps.bit_depth_chroma == 8 && first_mb < h.sp.mb_w * h.sp.mb_h;
+                sps.bit_depth_chroma == 8 && h.sp.mb_w <= AVR_MAX_MB_DIM && h.sp.mb_h <= AVR_MAX_MB_DIM &&
+                (int64_t)first_mb < (int64_t)h.sp.mb_w * (int64_t)h.sp.mb_h;
   *out = h;
   return true;
 }

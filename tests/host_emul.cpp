@@ -290,6 +290,24 @@ int main(int argc, char** argv) {
   std::string cmd = argv[1];
   std::vector<uint8_t> data;
   if (!read_file(argv[2], &data)) { fprintf(stderr, "cannot read %s\n", argv[2]); return 2; }
+  // scanraw <file> [seed flips]: the host front end (NAL scan, SPS/PPS/slice headers, block finder, recorder) on arbitrary or
+  // bit-flipped bytes -- headers included; must end with a status and stay inside its buffers (run under ASan/UBSan)
+  if (cmd == "scanraw") {
+    if (argc > 4) {
+      uint32_t x = (uint32_t)atoi(argv[3]) * 2654435761u + 99u;
+      for (int k = 0; k < atoi(argv[4]) && !data.empty(); k++) {
+        x = x * 1664525u + 1013904223u; const size_t span = (atoi(argv[3]) & 1) && data.size() > 96 ? 96 : data.size();   // odd seeds: SPS/PPS/first slice header only
+        const size_t pos = (x >> 8) % span;
+        x = x * 1664525u + 1013904223u; data[pos] ^= (uint8_t)(1u << ((x >> 13) & 7));
+      }
+    }
+    std::vector<uint8_t> exact(data);                       // heap block of the exact size: ASan sees any over-read
+    avr::FileRecord r1, r2; std::vector<avr::ScanSlice> coded;
+    const int rc1 = avr::scan_annexb(exact.data(), exact.size(), &r1, &coded);
+    const int rc2 = avr::record_annexb(exact.data(), exact.size(), &r2);
+    printf("TERMINATED scan=%d record=%d coded=%zu\n", rc1, rc2, coded.size());
+    return 0;
+  }
   avr::FileRecord rec;
   int rc = avr::record_annexb(data.data(), data.size(), &rec);
   if (rc) { fprintf(stderr, "record rc=%d\n", rc); return 1; }

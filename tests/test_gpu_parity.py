@@ -224,3 +224,79 @@ def test_baseline_config_shapes_roundtrip(ctx, tmpdir_path, shape):
     b.close(); rec.close()
     got = [blk["cabac"] for blk in parse_avrec(comp[0]) if "cabac" in blk]
     assert got == want
+
+
+IN_DOMAIN_SHAPES = [
+    dict(seed=61, mb_w=240, mb_h=135, frames=2, slices_per_frame=68, p_sig=150, p_cbf=230, p_cbp=240),   # config 5 geometry, no 8x8
+    dict(seed=62, mb_w=120, mb_h=68, frames=6, slices_per_frame=8, num_ref=3),                          # config 3 geometry
+    dict(seed=2, mb_w=120, mb_h=68, frames=5, slices_per_frame=1),                                       # config 2 geometry
+]
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("shape", IN_DOMAIN_SHAPES)
+def test_baseline_config_shapes_against_live_reference(ctx, tmpdir_path, shape):
+    """parity pinned at the benchmarked picture sizes.  In-domain variants (no 8x8 transform) of the
+    BASELINE config 2/3/5 shapes: our container == `oracle/_ref/recode compress` byte for byte (estimator halving after
+    long runs, key widths, > 1 M sort keys per file), the REFERENCE decompressor restores the input from OUR container,
+    and our decompressor restores it from the reference's."""
+    import avr_ctypes as A
+    clip = os.path.join(tmpdir_path, "cfg.h264")
+    data = gen_clip(clip, **shape)
+    ref_avrec = os.path.join(tmpdir_path, "ref.avrec")
+    rc, _, err = run([os.path.join(REF, "recode"), "compress", clip, ref_avrec], timeout=600)
+    assert rc == 0, err
+    want = open(ref_avrec, "rb").read()
+    comp, tc = A.compress_files(ctx, [data])
+    assert tc["bins"] > 1_000_000
+    assert comp[0] == want, "container differs from the reference compressor's"
+    ours = os.path.join(tmpdir_path, "ours.avrec")
+    open(ours, "wb").write(comp[0])
+    back_ref = os.path.join(tmpdir_path, "back_ref.h264")
+    rc, _, err = run([os.path.join(REF, "recode"), "decompress", ours, back_ref], timeout=600)
+    assert rc == 0, err
+    assert open(back_ref, "rb").read() == data, "reference decompressor does not restore the input from our container"
+    back, td = A.decompress_files(ctx, [want])
+    assert back[0] == data and td["bins"] == tc["bins"]
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_reference_decompressor_accepts_our_container(ctx, tmpdir_path, name):
+    """the survey's third oracle: a repo-written container fed to the reference DEcompressor (in-domain clips only: the
+    reference cannot invert 8x8 blocks)"""
+    import avr_ctypes as A
+    if name == "dct8x8":
+        pytest.skip("reference decompressor does not invert 8x8-transform streams (recode.cpp:1215-1219 vs 1485-1487)")
+    data = open(os.path.join(GOLDEN, name + ".h264"), "rb").read()
+    comp, _ = A.compress_files(ctx, [data])
+    p = os.path.join(tmpdir_path, "o.avrec")
+    open(p, "wb").write(comp[0])
+    back = os.path.join(tmpdir_path, "o.h264")
+    rc, _, err = run([os.path.join(REF, "recode"), "decompress", p, back], timeout=120)
+    assert rc == 0, err
+    assert open(back, "rb").read() == data
+
+
+@pytest.mark.parametrize("kind", ["empty", "junk", "sps_pps_only", "mp4ish"])
+def test_single_file_batches_without_coded_slices(ctx, tmpdir_path, kind):
+    """a batch in which NO file has a coded slice (ns == 0) crashed avr_cbatch_create_files; the reference writes
+    a literal-only container for such input"""
+    import avr_ctypes as A
+    clip = gen_clip(os.path.join(tmpdir_path, "s.h264"), seed=50, mb_w=2, mb_h=1, frames=2)
+    blob = {"empty": b"", "junk": b"junk that is not h264" * 10,
+            "sps_pps_only": clip[:clip.find(b"\x00\x00\x01\x65")] if b"\x00\x00\x01\x65" in clip else clip[:40],
+            "mp4ish": b"\x00\x00\x00\x18ftypmp42" + bytes(range(200))}[kind]
+    comp, _ = A.compress_files(ctx, [blob])
+    blocks = parse_avrec(comp[0])
+    assert all("cabac" not in b for b in blocks)
+    back, _ = A.decompress_files(ctx, comp)
+    assert back == [blob]
+    # the same through the CLI
+    exe = os.path.join(ROOT, "avrecode-ms_b200", "bin", "recode")
+    src, dst, rt = (os.path.join(tmpdir_path, n) for n in ("in.bin", "out.avrec", "rt.bin"))
+    open(src, "wb").write(blob)
+    assert run([exe, "compress", src, dst])[0] == 0
+    assert open(dst, "rb").read() == comp[0]
+    assert run([exe, "decompress", dst, rt])[0] == 0
+    assert open(rt, "rb").read() == blob

@@ -76,3 +76,19 @@ def test_corrupted_input_ends_with_a_status_inside_its_buffers(name, cmd):
     for seed, flips in ((1, 1), (2, 8), (3, 64), (4, 8)):
         rc, out, err = run([EMUL_ASAN, cmd, os.path.join(GOLDEN, name + ".h264"), str(seed), str(flips)], timeout=120)
         assert rc == 0 and b"TERMINATED" in out and b"runtime error" not in err and b"ERROR" not in err, out + err
+
+
+def test_header_fuzz_and_advisor_repro_stay_inside_buffers(tmpdir_path):
+    """`int id = br.ue()` let a 2^32-2 Exp-Golomb id through as a negative index (heap write before the Sps
+    table).  The 23-byte repro and bit flips over whole files (headers included) run through scan_annexb + record_annexb
+    under ASan/UBSan."""
+    repro = bytes.fromhex("0000016742001e0000030001" + "ff" * 10 + "80")
+    p = os.path.join(tmpdir_path, "repro.h264")
+    open(p, "wb").write(repro)
+    rc, out, err = run([EMUL_ASAN, "scanraw", p], timeout=60)
+    assert rc == 0 and b"TERMINATED" in out and b"ERROR" not in err and b"runtime error" not in err, out + err
+    # oversized picture: mb_w = 70000 must not size anything (unsupported -> literal), ue() ids at the type limit
+    for name in GOLDEN_NAMES:
+        for seed in range(1, 9):
+            rc, out, err = run([EMUL_ASAN, "scanraw", os.path.join(GOLDEN, name + ".h264"), str(seed), "24"], timeout=120)
+            assert rc == 0 and b"TERMINATED" in out and b"ERROR" not in err and b"runtime error" not in err, out + err
