@@ -235,7 +235,7 @@ struct avr_cbatch {
 
 extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs, int nfiles, avr_cbatch** out) {
   if (!ctx || !recs || nfiles < 0 || !out) return AVR_E_ARG;
-  if (nfiles > 1024) { avr_set_error("at most 1024 files per batch (sort key has 10 file bits)"); return AVR_E_ARG; }
+  if (nfiles > AVR_MAX_BATCH_FILES) { avr_set_error("at most %d files per batch (sort key has 13 file bits)", AVR_MAX_BATCH_FILES); return AVR_E_ARG; }
   CU(cudaSetDevice(ctx->device));
   avr_cbatch* b = new avr_cbatch();
   b->ctx = ctx; b->mem.arena = &ctx->arena;
@@ -284,7 +284,7 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
   d.nfiles = nfiles; d.nslices = (uint32_t)bsl.size(); d.nblocks = (uint32_t)nblocks; d.nbins = nbins;
   d.emit_cap = (uint32_t)emitted; d.tab = ctx->d_tab;
   int fb = 0; while ((1 << fb) < nfiles) fb++;
-  d.sort_end_bit = 22 + fb;
+  d.sort_end_bit = AVR_KEY_BITS + 1 + fb;
   // allocate
   AvrFileDesc* d_fds; uint16_t* d_bins; AvrBlock* d_blocks; AvrSlice* d_sl; AvrBatchSlice* d_bsl; AvrFrame* d_frames;
   DevMem& m = b->mem;
@@ -638,7 +638,7 @@ static std::mutex& files_registry_mu() { static std::mutex m; return m; }   // c
 extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* files, const size_t* lens, int nfiles,
                                        int host_threads, avr_cbatch** out, int* file_status) {
   if (!ctx || !files || !lens || nfiles < 0 || !out || !file_status) return AVR_E_ARG;
-  if (nfiles > 1024) { avr_set_error("at most 1024 files per batch (sort key has 10 file bits)"); return AVR_E_ARG; }
+  if (nfiles > AVR_MAX_BATCH_FILES) { avr_set_error("at most %d files per batch (sort key has 13 file bits)", AVR_MAX_BATCH_FILES); return AVR_E_ARG; }
   CU(cudaSetDevice(ctx->device));
   const double t_host0 = wall_ms();
   avr_trace(nullptr);
@@ -754,7 +754,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   d.nfiles = nfiles; d.nslices = (uint32_t)bsl.size(); d.nblocks = (uint32_t)nblocks; d.nbins = nbins; d.emit_cap = (uint32_t)emitted;
   d.tab = ctx->d_tab; d.bins = d_bins;
   int fb = 0; while ((1 << fb) < nfiles) fb++;
-  d.sort_end_bit = 22 + fb;
+  d.sort_end_bit = AVR_KEY_BITS + 1 + fb;
   AvrFileDesc* d_fds; AvrBlock* d_blocks; AvrBatchSlice* d_bsl; AvrFrame* d_frames; uint32_t* d_cnt; uint32_t* d_dst;
   if ((rc = m.alloc(&d_fds, fds.size())) || (rc = m.alloc(&d_blocks, nblocks)) || (rc = m.alloc(&d_bsl, bsl.size())) ||
       (rc = m.alloc(&d_frames, frames.size())) || (rc = tmp.alloc(&d_cnt, ns)) || (rc = tmp.alloc(&d_dst, ns)) ||

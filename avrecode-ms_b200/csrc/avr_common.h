@@ -60,24 +60,51 @@ typedef struct AvrFrame {
 
 // ---- estimator key space (dense re-indexing of reference model_key, recode.cpp:325,683-822,891)
 // default keys   : [0, 1026)                    key = ctx code
-// sig-map keys   : AVR_KEY_SIG_BASE + ((cat*64 + nnz)*64 + obs)*16 + zz_off
-//                  cat<14, nnz<64 (stored count, recode.cpp:928-931), obs<64, zz_off<16
-//                  one (cat, nnz, obs) row = 16 cells = one 32-byte sector: a block walks its rows in order
+// sig-map keys   : AVR_KEY_SIG_BASE + (row_base(cat) + row(stored, obs)) * 16 + zz_off, zz_off < 16
+//                  one (cat, stored, obs) row = 16 cells = one 32-byte sector; a block walks its rows in order (obs -> obs + 1
+//                  is the next row).  Only rows the model can reach exist (round 1 kept 14 x 64 x 64 rows = 1.8 MB per file,
+//                  most of them unreachable; a chain's working set then missed L1 and the batch's pools missed L2):
+//                    cats with <= 16 coefficients (all but 5, 9, 13): stored in 1..16, obs in 0..16 -> 17 x 17 rows
+//                    8x8 cats (5, 9, 13): stored = 0 is a FULL block (six-bit count, recode.cpp:928-931) with obs in 0..63;
+//                    stored in 1..63 has obs < stored (the EOB bin that follows one number `stored` is inferred and ends the
+//                    block, recode.cpp:1444-1445) -> 64 + 63*64/2 = 2080 rows
 // nnz-bit keys   : AVR_KEY_NZ_BASE + ((third*18 + nb18)*64 + (2^i + so_far))
 //                  third = is_8x8 + 2*is_dc + c422 + 4*cat  (<64), nb18 = prev + 2*left + 6*above (each of
 //                  left/above in 0..2), i<6, so_far<2^i: level i of a count's bit tree is the 2^i cells that start at
-//                  cell 2^i of the line (naturally aligned, so a level is ONE 2/4/8/16-byte load; cell 0 unused);
-//                  a 4-bit count stays inside one sector per neighbour class instead of 6 planes
+//                  cell 2^i of the line (naturally aligned; cell 0 unused); one 128-byte line per neighbour class
 // Bases are multiples of 64 cells and the per-file pool is a multiple of 128 bytes, so rows never straddle sectors.
+// 18 key bits: a compress sort key is (file << 19) | (key << 1) | symbol, which leaves 13 file bits in 32.
+#define AVR_SIG_ROWS_SMALL (17u * 17u)
+#define AVR_SIG_ROWS_8X8 (64u + 63u * 32u)
 #define AVR_KEY_SIG_BASE 1088u
-#define AVR_KEY_SIG_COUNT (14u * 64u * 64u * 16u)
-#define AVR_KEY_NZ_BASE (AVR_KEY_SIG_BASE + AVR_KEY_SIG_COUNT)
+#define AVR_KEY_SIG_COUNT ((11u * AVR_SIG_ROWS_SMALL + 3u * AVR_SIG_ROWS_8X8) * 16u)
+#define AVR_KEY_NZ_BASE ((AVR_KEY_SIG_BASE + AVR_KEY_SIG_COUNT + 63u) & ~63u)
 #define AVR_KEY_NZ_COUNT (64u * 18u * 64u)
 #define AVR_KEY_COUNT (AVR_KEY_NZ_BASE + AVR_KEY_NZ_COUNT)
-#define AVR_KEY_BITS 21
+#define AVR_KEY_BITS 18
+#define AVR_KEY_MASK ((1u << AVR_KEY_BITS) - 1u)
+#define AVR_MAX_BATCH_FILES 4096          /* sort key: 13 file bits; kernels are sized for this many chains per launch */
 
+static AVR_HD int avr_cat_is_8x8(int cat) { return cat == 5 || cat == 9 || cat == 13; }
+// first row of a category
+static AVR_HD uint32_t avr_sig_row_base(int cat) {
+  const uint32_t n8 = (uint32_t)(cat > 5) + (uint32_t)(cat > 9);
+  return ((uint32_t)cat - n8) * AVR_SIG_ROWS_SMALL + n8 * AVR_SIG_ROWS_8X8;
+}
+// row of (stored, obs) inside its category; out-of-model arguments are folded into the category (memory safety only)
+static AVR_HD uint32_t avr_sig_row(int cat, int stored, int obs) {
+  uint32_t s = (uint32_t)stored & 63u, o = (uint32_t)obs & 63u;
+  if (avr_cat_is_8x8(cat)) {
+    if (s == 0) return o;
+    if (o >= s) o = s - 1;
+    return 64u + s * (s - 1u) / 2u + o;
+  }
+  if (s > 16u) s = 16u;
+  if (o > 16u) o = 16u;
+  return s * 17u + o;
+}
 static AVR_HD uint32_t avr_key_sig(int cat, int nnz_stored, int obs, int zz_off) {
-  return AVR_KEY_SIG_BASE + ((((uint32_t)cat * 64u + (uint32_t)nnz_stored) * 64u + (uint32_t)obs) * 16u + (uint32_t)zz_off);
+  return AVR_KEY_SIG_BASE + (avr_sig_row_base(cat) + avr_sig_row(cat, nnz_stored, obs)) * 16u + ((uint32_t)zz_off & 15u);
 }
 static AVR_HD uint32_t avr_key_nz(int i, int so_far, int prev, int left, int above, int third) {
   return AVR_KEY_NZ_BASE + (((uint32_t)third * 18u + (uint32_t)(prev + 2 * left + 6 * above)) * 64u + ((1u << i) + (uint32_t)so_far));

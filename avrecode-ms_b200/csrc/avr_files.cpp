@@ -227,11 +227,11 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
   // AVR_HOST_PARSE=1 keeps the CABAC parse on the host cores (A/B measurement, bench.py)
   const char* hp = getenv("AVR_HOST_PARSE");
   if (!(hp && hp[0] == '1')) {
-    // batches: at most 1024 files and 192 MB of input each (~8.4 coded symbols per input byte on High-profile
+    // batches: at most AVR_MAX_BATCH_FILES files and 192 MB of input each (~8.4 coded symbols per input byte on High-profile
     // streams, the launch limit is 2^31); a batch that still exceeds the limit is halved (AVR_E_OVERFLOW)
     for (int i0 = 0; i0 < n && rc == AVR_OK;) {
       std::vector<int> ids; size_t bytes = 0;
-      for (; i0 < n && ids.size() < 1024 && (ids.empty() || bytes + in_len[i0] <= (192u << 20)); i0++) { ids.push_back(i0); bytes += in_len[i0]; }
+      for (; i0 < n && ids.size() < AVR_MAX_BATCH_FILES && (ids.empty() || bytes + in_len[i0] <= (192u << 20)); i0++) { ids.push_back(i0); bytes += in_len[i0]; }
       rc = compress_device_parse(ctx, in, in_len, ids, host_threads, containers, done, &tt);
     }
     if (rc != AVR_OK) return rc;
@@ -255,7 +255,7 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
     std::vector<int> files;
     uint64_t sym = 0;
     size_t i = r0;
-    for (; i < rest.size() && files.size() < 1024; i++) {
+    for (; i < rest.size() && files.size() < AVR_MAX_BATCH_FILES; i++) {
       const int f = rest[i];
       if (rec_rc[f]) continue;
       uint64_t e = avr_record_view(recs[f])->emitted;

@@ -30,7 +30,7 @@ struct AvrDevBatch {
   uint16_t* prob;                  // [emit_cap]
   uint32_t emit_cap;               // exact number of coded symbols (host computes it while staging)
   void* cub_tmp; size_t cub_tmp_bytes;
-  int sort_end_bit;                // 22 + bits(nfiles)
+  int sort_end_bit;                // AVR_KEY_BITS + 1 + bits(nfiles)
   // outputs
   uint8_t* scratch; const uint64_t* scratch_off; const uint32_t* scratch_cap;
   uint32_t* out_len; int* status;

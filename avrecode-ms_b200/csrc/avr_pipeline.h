@@ -35,7 +35,7 @@ struct AvrPipe {
   const AvrFrame* frames;
   uint8_t* store;          // per-picture nnz stores of the whole batch, zeroed before pass A
   uint32_t* seg;           // [nblocks + nslices + 1] segment sizes, then (scanned) emitted positions
-  uint32_t* keys;          // [nemit] (file << 22) | (key << 1) | symbol, emission order
+  uint32_t* keys;          // [nemit] (file << (AVR_KEY_BITS + 1)) | (key << 1) | symbol, emission order
   uint32_t nemit;
   uint16_t* prob;          // [nemit] pass C output
   const AvrTables* tab;
@@ -74,7 +74,7 @@ static AVR_HD uint32_t avr_pass_count(const AvrBlock& blk, uint32_t seg_end_bin,
 }
 
 // ---- pass B: keys of one segment, written at the segment's emitted position ----------------
-// out[i] = (file << 22) | (key << 1) | symbol
+// out[i] = (file << (AVR_KEY_BITS + 1)) | (key << 1) | symbol
 static AVR_HD void avr_pass_keys_default(const uint16_t* bins, uint32_t b0, uint32_t b1, uint32_t filebits, uint32_t* out) {
   for (uint32_t i = b0; i < b1; i++) {
     uint16_t rec = bins[i];
@@ -205,7 +205,7 @@ static AVR_HD void avr_body_keys(const AvrPipe& a, uint32_t e) {
   const AvrFileDesc& fd = a.fds[sl.file];
   const uint16_t* bins = a.bins + fd.bin_off;
   uint32_t* out = a.keys + a.seg[e];
-  const uint32_t filebits = sl.file << 22;
+  const uint32_t filebits = sl.file << (AVR_KEY_BITS + 1);
   if (e == sl.block_start + s) {
     uint32_t end = sl.block_start < sl.block_end ? a.blocks[sl.block_start].bin_start : sl.bin_end;
     avr_pass_keys_default(bins, sl.bin_start, end, filebits, out);
@@ -232,7 +232,7 @@ static AVR_HD uint32_t avr_ones_between(const uint32_t* P, uint32_t first, uint3
 // element of the fn scan: bit 31 of kflag = starts a key run
 struct AvrHalfSeg { uint32_t a, kflag; };
 static AVR_HD AvrHalfSeg avr_fn_element(uint32_t i, const uint32_t* sorted, const uint32_t* head, const uint32_t* P) {
-  const uint32_t key = (sorted[i] >> 1) & 0x1FFFFFu;
+  const uint32_t key = (sorted[i] >> 1) & AVR_KEY_MASK;
   const uint32_t h = head[i], r = i - h;
   const AvrPeriod p = avr_period_of(key);
   AvrHalfSeg e;
@@ -257,7 +257,7 @@ struct AvrMaxOp { AVR_HD uint32_t operator()(uint32_t a, uint32_t b) const { ret
 
 static AVR_HD void avr_body_estimate(uint32_t i, const uint32_t* sorted, const uint32_t* idx, const uint32_t* head,
                                      const uint32_t* P, const AvrHalfSeg* fn, uint16_t* prob) {
-  const uint32_t w = sorted[i], sym = w & 1, key = (w >> 1) & 0x1FFFFFu;
+  const uint32_t w = sorted[i], sym = w & 1, key = (w >> 1) & AVR_KEY_MASK;
   const uint32_t h = head[i], r = i - h;
   const AvrPeriod p = avr_period_of(key);
   uint32_t ob = 0, pos0 = 1;

@@ -266,7 +266,7 @@ def test_reference_decompressor_accepts_our_container(ctx, tmpdir_path, name):
     """the survey's third oracle: a repo-written container fed to the reference DEcompressor (in-domain clips only: the
     reference cannot invert 8x8 blocks)"""
     import avr_ctypes as A
-    if name == "dct8x8":
+    if name in ("dct8x8", "dense_full_blocks"):    # both generated with transform_8x8=1 (tests/golden/make_golden.py)
         pytest.skip("reference decompressor does not invert 8x8-transform streams (recode.cpp:1215-1219 vs 1485-1487)")
     data = open(os.path.join(GOLDEN, name + ".h264"), "rb").read()
     comp, _ = A.compress_files(ctx, [data])
