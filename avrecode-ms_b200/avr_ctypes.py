@@ -22,7 +22,7 @@ EXPORTS = [
     "avr_cbatch_create", "avr_cbatch_create_files", "avr_cbatch_span_count", "avr_cbatch_span", "avr_cbatch_run", "avr_cbatch_fetch", "avr_cbatch_payload", "avr_cbatch_timing",
     "avr_cbatch_destroy", "avr_dbatch_create", "avr_dbatch_run", "avr_dbatch_fetch", "avr_dbatch_slice",
     "avr_dbatch_timing", "avr_dbatch_destroy", "avr_compress_files", "avr_decompress_files", "avr_buffer_free",
-    "avr_streams_encode", "avr_streams_decode",
+    "avr_streams_encode", "avr_streams_decode", "avr_streams_encode_static",
 ]
 STREAM_FIXED_HALF = 0
 STREAM_ADAPTIVE = 1
@@ -104,6 +104,8 @@ def lib():
                                          C.POINTER(C.c_uint64), C.POINTER(Timing)]
         L.avr_streams_decode.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64), C.c_uint32, C.c_uint32, C.c_int, C.c_int,
                                          C.c_char_p, C.POINTER(Timing)]
+        L.avr_streams_encode_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
+                                                C.c_uint64, C.c_void_p]
         _lib = L
     return _lib
 
@@ -328,3 +330,16 @@ def streams_decode(ctx, coded, nstreams, nbins, digit_bits=16, model=STREAM_FIXE
     t = Timing()
     _check(lib().avr_streams_decode(ctx.h, b"".join(coded), off, nstreams, nbins, digit_bits, model, out, C.byref(t)))
     return out.raw[:nstreams * nbins], t.as_dict()
+
+
+STREAMS_STATIC_SCRATCH_BYTES = 8 << 20
+
+
+def streams_coded_bound(nbins, model):
+    """AVR_STREAMS_CODED_BOUND of include/avrecode_b200.h"""
+    return (((nbins // 8 + 32) if model == STREAM_FIXED_HALF else (nbins + 32)) + 15) & ~15
+
+
+def streams_encode_static(ctx, d_bits_ptr, nstreams, nbins, digit_bits, model, d_coded_ptr, coded_cap, d_coded_off_ptr):
+    """avr_streams_encode_static: raw DEVICE pointers (ints) in and out; allocates nothing.  Returns the C return code."""
+    return lib().avr_streams_encode_static(ctx.h, d_bits_ptr, nstreams, nbins, digit_bits, model, d_coded_ptr, coded_cap, d_coded_off_ptr)

@@ -177,3 +177,91 @@ done:
   for (auto& e : ev) if (e) cudaEventDestroy(e);
   return rc;
 }
+
+// ---- avr_streams_encode_static: the encode above for callers that may not allocate ------------------------------
+// No counterpart in the reference (include/avrecode_b200.h).
+// Same kernels as avr_streams_encode (avr_k_stream_encode, scratch-offset fill, exclusive scan + gather); what differs
+// is where the intermediate buffers live: the per-stream scratch, lengths, status words and offsets are carved out of
+// ONE file-scope device array instead of cudaMalloc'ed blocks.  Every GPU that loads this library holds the array
+// until the process exits.  All calls share it (it keeps the previous call's contents): calls that overlap on the GPU
+// race, and the words that must start at zero are cleared by every call.
+static __device__ __align__(256) unsigned char g_streams_static_scratch[AVR_STREAMS_STATIC_SCRATCH_BYTES];
+
+// In host code `g_streams_static_scratch` is a host-side stand-in, not a device address: the device address is asked
+// for once per device, with that device current, and cached.
+#include <mutex>
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[64];
+static int static_scratch_ptr(int device, unsigned char** out) {
+  if (device < 0 || device >= 64) { avr_set_error("streams_static: device %d out of range", device); return AVR_E_ARG; }
+  std::lock_guard<std::mutex> g(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_streams_static_scratch);      // the caller made `device` current
+    if (e != cudaSuccess || !p) { avr_set_error("streams_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return AVR_E_CUDA; }
+    g_static_ptr[device] = (unsigned char*)p;
+  }
+  *out = g_static_ptr[device];
+  return AVR_OK;
+}
+// first non-zero status of the streams -> *first (cleared by the caller)
+__global__ void __launch_bounds__(256) avr_k_stream_first_status(const int* status, uint32_t n, int* first) {
+  const uint32_t s = blockIdx.x * 256 + threadIdx.x;
+  if (s < n && status[s]) atomicCAS(first, 0, status[s]);
+}
+
+extern "C" int avr_streams_encode_static(avr_context* ctx, const uint8_t* d_bits, uint32_t nstreams, uint32_t nbins, int digit_bits,
+                                         int model, uint8_t* d_coded, uint64_t coded_cap, uint64_t* d_coded_off) {
+  int rc = check_args(ctx, nstreams, nbins, digit_bits, model);
+  if (rc) return rc;
+  if (!d_coded_off || (nstreams && (!d_coded || (!d_bits && nbins)))) { avr_set_error("streams_static: null argument"); return AVR_E_ARG; }
+  const uint32_t cap = avr_stream_cap(nbins, model);
+  // layout inside the array (every part 256-byte aligned)
+  auto up = [](uint64_t x) { return (x + 255) & ~255ull; };
+  const uint64_t o_div = 0, o_first = up(sizeof(AvrDivTab)), o_len = o_first + 256, o_status = o_len + up(4ull * nstreams),
+                 o_soff = o_status + up(4ull * nstreams), o_scratch = o_soff + up(8ull * nstreams);
+  const uint64_t need = o_scratch + (uint64_t)nstreams * cap;
+  if (need > AVR_STREAMS_STATIC_SCRATCH_BYTES) {
+    avr_set_error("streams_static: %u streams x %u bins need %llu bytes of scratch, the static array holds %u (use avr_streams_encode)",
+                  nstreams, nbins, (unsigned long long)need, (unsigned)AVR_STREAMS_STATIC_SCRATCH_BYTES);
+    return AVR_E_ARG;
+  }
+  if (coded_cap < (uint64_t)nstreams * cap) {
+    avr_set_error("streams_static: coded_cap %llu < nstreams * AVR_STREAMS_CODED_BOUND = %llu", (unsigned long long)coded_cap,
+                  (unsigned long long)nstreams * cap);
+    return AVR_E_ARG;
+  }
+  if (cudaSetDevice(avr_context_device(ctx)) != cudaSuccess) { avr_set_error("streams_static: cudaSetDevice failed"); return AVR_E_CUDA; }
+  unsigned char* base = nullptr;
+  if ((rc = static_scratch_ptr(avr_context_device(ctx), &base))) return rc;
+  cudaStream_t st = (cudaStream_t)avr_context_stream(ctx);
+  AvrDivTab* d_div = (AvrDivTab*)(base + o_div);
+  int* d_first = (int*)(base + o_first);
+  uint32_t* d_len = (uint32_t*)(base + o_len);
+  int* d_status = (int*)(base + o_status);
+  uint64_t* d_soff = (uint64_t*)(base + o_soff);
+  uint8_t* d_scratch = base + o_scratch;
+  static const AvrDivTab h_div = AVR_DIV_TAB_INIT;
+  int first = 0;
+  CU(cudaMemsetAsync(d_first, 0, 256, st));                                  // must start at zero; the rest is overwritten before it is read
+  if (nstreams == 0) { CU(cudaMemsetAsync(d_coded_off, 0, sizeof(uint64_t), st)); CU(cudaStreamSynchronize(st)); return AVR_OK; }
+  CU(cudaMemcpyAsync(d_div, &h_div, sizeof h_div, cudaMemcpyHostToDevice, st));
+  {
+    const uint32_t grid = (nstreams + AVR_STREAM_BLOCK - 1) / AVR_STREAM_BLOCK;
+#define LAUNCH_ENC(D, M) avr_k_stream_encode<D, M><<<grid, AVR_STREAM_BLOCK, 0, st>>>(d_bits, nstreams, nbins, d_div, d_scratch, cap, d_len, d_status)
+    if (digit_bits == 8) { if (model == AVR_STREAM_ADAPTIVE) LAUNCH_ENC(8, AVR_STREAM_ADAPTIVE); else LAUNCH_ENC(8, AVR_STREAM_FIXED_HALF); }
+    else { if (model == AVR_STREAM_ADAPTIVE) LAUNCH_ENC(16, AVR_STREAM_ADAPTIVE); else LAUNCH_ENC(16, AVR_STREAM_FIXED_HALF); }
+#undef LAUNCH_ENC
+    CU(cudaGetLastError());
+    avr_k_stream_scratch_off<<<(nstreams + 255) / 256, 256, 0, st>>>(d_soff, nstreams, cap);
+    const int lrc = avr_launch_compact(d_scratch, d_soff, d_len, d_coded_off, d_coded_off + nstreams, d_coded, nstreams, st);
+    if (lrc) { avr_set_error("streams_static: compaction failed (%d)", lrc); return AVR_E_CUDA; }
+    avr_k_stream_first_status<<<(nstreams + 255) / 256, 256, 0, st>>>(d_status, nstreams, d_first);
+    CU(cudaGetLastError());
+  }
+  CU(cudaMemcpyAsync(&first, d_first, sizeof first, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (first) { avr_set_error("streams_static: a stream failed with %d", first); rc = first; }
+done:
+  return rc;
+}

@@ -157,6 +157,26 @@ int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_t nstreams,
 int avr_streams_decode(avr_context* ctx, const uint8_t* coded, const uint64_t* coded_off, uint32_t nstreams, uint32_t nbins,
                        int digit_bits, int model, uint8_t* bits_out, avr_timing* t);
 
+/* ---- streams, no-allocation variant ------------------------------------------------------------------------ */
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  avr_streams_encode with
+ * DEVICE buffers in and out and every intermediate buffer (per-stream scratch, lengths, status, offsets) inside one
+ * file-scope `static __device__` array of AVR_STREAMS_STATIC_SCRATCH_BYTES that each GPU loading the library holds until
+ * the process exits.  The call makes no cudaMalloc / cudaFree / host allocation and launches on the context's stream,
+ * which it synchronises before returning.
+ *   d_bits       device, nstreams * nbins bytes, stream-major, one byte per bin (zero / non-zero)
+ *   d_coded      device, coded_cap >= nstreams * AVR_STREAMS_CODED_BOUND(nbins, model) bytes; the streams back to back
+ *   d_coded_off  device, nstreams + 1 entries: where each stream begins, [nstreams] = total bytes
+ * Limit: (nstreams * AVR_STREAMS_CODED_BOUND + 20 * nstreams + ~2 KB) <= AVR_STREAMS_STATIC_SCRATCH_BYTES, else AVR_E_ARG
+ * with the sizes in avr_last_error() (use avr_streams_encode for larger batches).  All calls share the array, which
+ * keeps the previous call's contents (the call clears what must start at zero): calls that overlap on the GPU -- two
+ * contexts of one device, two host threads -- race and must be serialised by the caller. */
+#define AVR_STREAMS_STATIC_SCRATCH_BYTES (8u << 20)
+#define AVR_STREAMS_CODED_BOUND(nbins, model) \
+  (((((model) == AVR_STREAM_FIXED_HALF) ? (uint64_t)(nbins) / 8 + 32 : (uint64_t)(nbins) + 32) + 15) & ~(uint64_t)15)
+int avr_streams_encode_static(avr_context* ctx, const uint8_t* d_bits, uint32_t nstreams, uint32_t nbins, int digit_bits,
+                              int model, uint8_t* d_coded, uint64_t coded_cap, uint64_t* d_coded_off);
+
 #ifdef __cplusplus
 }
 #endif
