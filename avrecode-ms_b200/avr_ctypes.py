@@ -21,8 +21,8 @@ EXPORTS = [
     "avr_rec_end_coding_type", "avr_rec_bin", "avr_record_annexb", "avr_record_counts", "avr_record_span",
     "avr_cbatch_create", "avr_cbatch_create_files", "avr_cbatch_span_count", "avr_cbatch_span", "avr_cbatch_run", "avr_cbatch_fetch", "avr_cbatch_payload", "avr_cbatch_timing",
     "avr_cbatch_destroy", "avr_dbatch_create", "avr_dbatch_run", "avr_dbatch_fetch", "avr_dbatch_slice",
-    "avr_dbatch_timing", "avr_dbatch_destroy", "avr_compress_files", "avr_decompress_files", "avr_buffer_free",
-    "avr_streams_encode", "avr_streams_decode", "avr_streams_encode_static",
+    "avr_dbatch_timing", "avr_dbatch_destroy", "avr_compress_files", "avr_decompress_files", "avr_buffer_free", "avr_compress_files_multi", "avr_decompress_files_multi",
+    "avr_streams_encode", "avr_streams_decode", "avr_streams_encode_static", "avr_measure_recurrence_floor",
 ]
 STREAM_FIXED_HALF = 0
 STREAM_ADAPTIVE = 1
@@ -99,6 +99,8 @@ def lib():
         L.avr_compress_files.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_size_t), C.c_int, C.c_int,
                                          C.POINTER(Buffer), C.POINTER(Timing)]
         L.avr_decompress_files.argtypes = L.avr_compress_files.argtypes
+        L.avr_compress_files_multi.argtypes = [C.POINTER(C.c_void_p), C.c_int] + L.avr_compress_files.argtypes[1:]
+        L.avr_decompress_files_multi.argtypes = L.avr_compress_files_multi.argtypes
         L.avr_buffer_free.argtypes = [C.POINTER(Buffer)]
         L.avr_streams_encode.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.POINTER(Buffer),
                                          C.POINTER(C.c_uint64), C.POINTER(Timing)]
@@ -106,6 +108,7 @@ def lib():
                                          C.c_char_p, C.POINTER(Timing)]
         L.avr_streams_encode_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                                 C.c_uint64, C.c_void_p]
+        L.avr_measure_recurrence_floor.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -276,6 +279,27 @@ class FileResults:
         self.close()
 
 
+class _Multi:
+    """adapter: fn(ctxs, nctx, ...) behind the single-context call shape of _files_call"""
+
+    def __init__(self, fn, ctxs):
+        self.fn, self.arr, self.n = fn, (C.c_void_p * len(ctxs))(*[c.h for c in ctxs]), len(ctxs)
+        self.h = None
+
+    def __call__(self, _h, *rest):
+        return self.fn(self.arr, self.n, *rest)
+
+
+def compress_files_multi(ctxs, blobs, threads=0, copy=True):
+    m = _Multi(lib().avr_compress_files_multi, ctxs)
+    return _files_call(m, m, blobs, threads or (os.cpu_count() or 1), copy)
+
+
+def decompress_files_multi(ctxs, blobs, threads=0, copy=True):
+    m = _Multi(lib().avr_decompress_files_multi, ctxs)
+    return _files_call(m, m, blobs, threads or (os.cpu_count() or 1), copy)
+
+
 def _files_call(fn, ctx, blobs, threads, copy=True):
     n = len(blobs)
     ins = (C.c_void_p * n)()
@@ -343,3 +367,10 @@ def streams_coded_bound(nbins, model):
 def streams_encode_static(ctx, d_bits_ptr, nstreams, nbins, digit_bits, model, d_coded_ptr, coded_cap, d_coded_off_ptr):
     """avr_streams_encode_static: raw DEVICE pointers (ints) in and out; allocates nothing.  Returns the C return code."""
     return lib().avr_streams_encode_static(ctx.h, d_bits_ptr, nstreams, nbins, digit_bits, model, d_coded_ptr, coded_cap, d_coded_off_ptr)
+
+
+def recurrence_floor(ctx, steps=1 << 20):
+    """SM cycles per bin of the bare low/range recurrence on one thread (avr_measure_recurrence_floor)."""
+    v = C.c_double()
+    _check(lib().avr_measure_recurrence_floor(ctx.h, steps, C.byref(v)))
+    return v.value

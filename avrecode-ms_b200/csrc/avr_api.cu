@@ -5,6 +5,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <algorithm>
@@ -29,10 +30,14 @@ extern "C" int avr_version(void) { return 100; }
 // Device blocks released by a batch stay with the context and are handed to the next batch: cudaMalloc /
 // cudaFree of multi-GB buffers cost 50-200 ms per batch, more than some of the kernels.  Everything runs on
 // the context's one stream and batches synchronise before they release, so reuse needs no extra ordering.
+// The lanes of one context (avr_context_lane) share ONE arena: a block released by a batch of one lane serves the next batch
+// of any lane (separate caches doubled the footprint and ran a 180 GB device out of memory), hence the lock.
 struct AvrArena {
   std::vector<std::pair<size_t, void*>> free_blocks;
   size_t cached = 0;
+  std::mutex mu;
   void* take(size_t n, size_t* got) {
+    std::lock_guard<std::mutex> g(mu);
     size_t best = (size_t)-1, bi = 0;
     for (size_t i = 0; i < free_blocks.size(); i++) {
       const size_t sz = free_blocks[i].first;
@@ -44,8 +49,8 @@ struct AvrArena {
     free_blocks.erase(free_blocks.begin() + bi);
     return p;
   }
-  void give(void* p, size_t n) { free_blocks.push_back({n, p}); cached += n; }
-  void flush() { for (auto& b : free_blocks) cudaFree(b.second); free_blocks.clear(); cached = 0; }
+  void give(void* p, size_t n) { std::lock_guard<std::mutex> g(mu); free_blocks.push_back({n, p}); cached += n; }
+  void flush() { std::lock_guard<std::mutex> g(mu); for (auto& b : free_blocks) cudaFree(b.second); free_blocks.clear(); cached = 0; }
 };
 // Page-locked host staging, cached the same way: D2H into pageable memory goes through the driver's own bounce
 // buffers at a third of the bandwidth, and a fresh std::vector of the payload size is zero-filled first.
@@ -74,8 +79,10 @@ struct avr_context {
   cudaStream_t stream;
   AvrTables* d_tab;
   cudaEvent_t ev[4];
-  AvrArena arena;
+  AvrArena arena_own;
+  AvrArena* arena = &arena_own;           // twins point at their parent's
   AvrPinned pinned;
+  std::vector<avr_context*> twins;        // further lanes on the same device (own stream, events, caches): avr_context_lane
 };
 
 extern "C" int avr_context_create(int device, avr_context** out) {
@@ -106,8 +113,10 @@ extern "C" int avr_context_create(int device, avr_context** out) {
 }
 extern "C" void avr_context_destroy(avr_context* c) {
   if (!c) return;
+  for (avr_context* t : c->twins) avr_context_destroy(t);
+  c->twins.clear();
   cudaSetDevice(c->device);
-  c->arena.flush(); c->pinned.flush();
+  c->arena_own.flush(); c->pinned.flush();
   if (c->d_tab) cudaFree(c->d_tab);
   for (auto& e : c->ev) if (e) cudaEventDestroy(e);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -115,6 +124,20 @@ extern "C" void avr_context_destroy(avr_context* c) {
 }
 extern "C" void* avr_context_stream(avr_context* c) { return c ? (void*)c->stream : nullptr; }
 int avr_context_device(const avr_context* c) { return c ? c->device : -1; }
+// Lane k of a context: k = 0 is the context itself, k >= 1 a twin on the same device with its own stream, events, device-block
+// and pinned caches, created on first use and destroyed with the context.  The file-level calls run sub-batches on several
+// lanes so that one batch's copies and host work overlap another batch's kernels (avr_files.cpp).  Call from one thread.
+avr_context* avr_context_lane(avr_context* c, int k) {
+  if (!c || k < 0) return nullptr;
+  if (k == 0) return c;
+  while ((int)c->twins.size() < k) {
+    avr_context* t = nullptr;
+    if (avr_context_create(c->device, &t) != AVR_OK) return nullptr;
+    t->arena = c->arena;
+    c->twins.push_back(t);
+  }
+  return c->twins[(size_t)k - 1];
+}
 
 // ---- recorder bindings ------------------------------------------------------------------------
 struct avr_record {
@@ -238,7 +261,7 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
   if (nfiles > AVR_MAX_BATCH_FILES) { avr_set_error("at most %d files per batch (sort key has 13 file bits)", AVR_MAX_BATCH_FILES); return AVR_E_ARG; }
   CU(cudaSetDevice(ctx->device));
   avr_cbatch* b = new avr_cbatch();
-  b->ctx = ctx; b->mem.arena = &ctx->arena;
+  b->ctx = ctx; b->mem.arena = ctx->arena;
   memset(&b->d, 0, sizeof b->d);
   memset(&b->t, 0, sizeof b->t);
   std::vector<AvrFileDesc> fds((size_t)nfiles);
@@ -445,7 +468,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   if (!ctx || (!slices && nfiles) || !per_file || nfiles < 0 || !out) return AVR_E_ARG;
   CU(cudaSetDevice(ctx->device));
   avr_dbatch* b = new avr_dbatch();
-  b->ctx = ctx; b->mem.arena = &ctx->arena;
+  b->ctx = ctx; b->mem.arena = ctx->arena;
   memset(&b->d, 0, sizeof b->d);
   memset(&b->t, 0, sizeof b->t);
   std::vector<AvrFileDesc> fds((size_t)nfiles);
@@ -673,9 +696,9 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
     }
   }
   avr_cbatch* b = new avr_cbatch();
-  b->ctx = ctx; b->mem.arena = &ctx->arena; memset(&b->d, 0, sizeof b->d); memset(&b->t, 0, sizeof b->t);
+  b->ctx = ctx; b->mem.arena = ctx->arena; memset(&b->d, 0, sizeof b->d); memset(&b->t, 0, sizeof b->t);
   DevMem& m = b->mem;
-  DevMem tmp; tmp.arena = &ctx->arena;   // returned to the context before this call ends
+  DevMem tmp; tmp.arena = ctx->arena;   // returned to the context before this call ends
   auto fail = [&](int r) { tmp.release(); m.release(); delete b; delete bf; return r; };
   const uint32_t ns = (uint32_t)ps.size();
   uint8_t* d_raw; uint16_t* d_bins; AvrBlock* d_blkpool; avr::MbInfo* d_rows; uint64_t* d_row_off; AvrParseSlice* d_ps; AvrParseResult* d_res;

@@ -11,3 +11,6 @@ uint32_t avr_span_flip(const avr::FileRecord& rec, uint32_t span_index);
 void avr_trace(const char* what);
 struct avr_context;
 int avr_context_device(const avr_context* ctx);   // CUDA device ordinal of the context
+avr_context* avr_context_lane(avr_context* ctx, int k);   // lane k of a context (0 = itself), created on first use
+// chains that will be resident at the same time across concurrent decompress launches (carve-out sizing); 0 = this launch only
+void avr_set_chain_concurrency_hint(int files);

@@ -26,6 +26,17 @@
 #define AVR_RING (1u << AVR_RING_LOG)
 #define AVR_RING_EMPTY 0xFFFFFFFFu
 #define AVR_REC_ABORT 2047u          // ctx code: chain failed, encoder must stop
+#define AVR_REC_NOP 2046u            // ctx code: padding up to the end of a batch, ignored
+#if defined(AVR_ENC_BATCH)
+#define AVR_RING_BATCH 32u           // the encoder takes records in aligned batches of this many (one probe per batch)
+#endif
+
+// diagnostic builds only (tools/gpu_ab2.sh): AVR_DIAG_NOENC = the encoder warp does nothing and the chain never waits for it
+#if defined(AVR_DIAG_NOENC)
+#define AVR_DIAG_WAIT(c) false
+#else
+#define AVR_DIAG_WAIT(c) (c)
+#endif
 
 struct AvrCabRegs {                  // CABAC encoder state (registers of the encoder thread)
   uint32_t low, range, n, cap;
@@ -39,7 +50,7 @@ struct AvrDecShared {
   AvrMs ms[98];                                // hot.div again, one entry per total
   uint16_t est_def[AVR_NUM_CTX_KEYS + 2];      // estimators of the 1026 default keys (file lifetime)
   uint8_t st[1024];                            // CABAC context states of the current slice (encoder thread)
-  uint32_t ring[AVR_RING];                     // (ctx << 1) | symbol, or AVR_RING_EMPTY; the consumer empties what it has read
+  alignas(16) uint32_t ring[AVR_RING];         // (ctx << 1) | symbol, or AVR_RING_EMPTY; the consumer empties what it has read
   uint32_t ring_head, ring_tail_seen;          // producer side
   volatile uint32_t ring_tail;                 // consumer progress (back-pressure)
   // range decoder (arithmetic_code.h:220-288)
@@ -130,7 +141,7 @@ AVR_DEC_INL int avr_cab_consume(AvrCabRegs& c, uint32_t rec) {
     avr_cab_finish(c);
     return 1;
   }
-  return 1;                                                   // AVR_REC_ABORT
+  return ctx == AVR_REC_NOP ? 0 : 1;                          // padding / AVR_REC_ABORT
 }
 
 // ---- ring -----------------------------------------------------------------------------------------
@@ -139,13 +150,14 @@ AVR_DEC_INL void avr_ring_post(uint32_t ctx, int symbol) {
   const uint32_t head = g_dec.ring_head;
   if (head - g_dec.ring_tail_seen >= AVR_RING - 1) {          // full: wait for the encoder
     uint32_t t;
-    do { t = g_dec.ring_tail; } while (head - t >= AVR_RING - 1);
+    do { t = g_dec.ring_tail; } while (AVR_DIAG_WAIT(head - t >= AVR_RING - 1));
     g_dec.ring_tail_seen = t;
   }
   reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (ctx << 1) | (uint32_t)symbol;
   g_dec.ring_head = head + 1;
 #else
   avr_cab_consume(g_cab_host, (ctx << 1) | (uint32_t)symbol);
+  g_dec.ring_head++;
 #endif
 }
 
@@ -154,7 +166,7 @@ AVR_DEC_INL void avr_ring_post_r(uint32_t& head, uint32_t& tail_seen, uint32_t c
 #if defined(__CUDACC__)
   if (head - tail_seen >= AVR_RING - 1) {
     uint32_t t;
-    do { t = g_dec.ring_tail; } while (head - t >= AVR_RING - 1);
+    do { t = g_dec.ring_tail; } while (AVR_DIAG_WAIT(head - t >= AVR_RING - 1));
     tail_seen = t;
   }
   reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (ctx << 1) | (uint32_t)symbol;
@@ -165,23 +177,54 @@ AVR_DEC_INL void avr_ring_post_r(uint32_t& head, uint32_t& tail_seen, uint32_t c
 #endif
 }
 
+#if !defined(AVR_ENC_SLEEP)
+#define AVR_ENC_SLEEP 32
+#endif
 #if defined(__CUDACC__)
 // Encoder thread: consumes the slice's records until end_of_slice / abort.
 static __device__ __noinline__ void avr_cab_encoder_thread(uint8_t* out, uint32_t cap) {
   AvrCabRegs c;
   c.low = 0; c.range = (1u << 22) * 0x1FEu; c.n = 0; c.cap = cap; c.out = out; c.err = 0;   // cabac_code.h:30
   uint32_t tail = g_dec.ring_tail;
+#if defined(AVR_DIAG_NOENC)
+  g_dec.cab_n = 0; g_dec.cab_err = 0; (void)tail; (void)c;
+  return;
+#endif
+#if defined(AVR_ENC_BATCH)
+  // Records are taken in aligned batches of AVR_RING_BATCH: slots are filled in order, so ONE probe of the batch's last
+  // slot says that the whole batch is there, and the encoder sleeps (instead of spinning on every slot) while the slower
+  // chain fills it.  The chain pads a slice's last batch with NOP records.
+  volatile uint32_t* ring = reinterpret_cast<volatile uint32_t*>(g_dec.ring);
+  bool finished = false;
+  while (!finished) {
+    const uint32_t probe = (tail + AVR_RING_BATCH - 1) & (AVR_RING - 1);
+    while (ring[probe] == AVR_RING_EMPTY) __nanosleep(AVR_ENC_SLEEP);
+    for (uint32_t k = 0; k < AVR_RING_BATCH; k += 4) {
+      const uint32_t sa = (uint32_t)__cvta_generic_to_shared(&g_dec.ring[(tail + k) & (AVR_RING - 1)]);
+      uint4 q;
+      asm volatile("ld.volatile.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "r"(sa) : "memory");
+      asm volatile("st.volatile.shared.v4.u32 [%0], {%1, %1, %1, %1};" ::"r"(sa), "r"(AVR_RING_EMPTY) : "memory");
+      if (!finished) finished = avr_cab_consume(c, q.x) != 0;
+      if (!finished) finished = avr_cab_consume(c, q.y) != 0;
+      if (!finished) finished = avr_cab_consume(c, q.z) != 0;
+      if (!finished) finished = avr_cab_consume(c, q.w) != 0;
+    }
+    tail += AVR_RING_BATCH;
+    g_dec.ring_tail = tail;            // after the slots were emptied: the producer reuses a slot only after it has seen the tail pass it
+  }
+#else
   volatile uint32_t* ring = reinterpret_cast<volatile uint32_t*>(g_dec.ring);
   for (;;) {
     const uint32_t slot = tail & (AVR_RING - 1);
     uint32_t rec = ring[slot];
-    while (rec == AVR_RING_EMPTY) { __nanosleep(32); rec = ring[slot]; }
+    while (rec == AVR_RING_EMPTY) { __nanosleep(AVR_ENC_SLEEP); rec = ring[slot]; }
     ring[slot] = AVR_RING_EMPTY;       // before the tail moves: the producer reuses a slot only after it has seen the tail pass it
     tail++;
     if ((tail & 63) == 0) g_dec.ring_tail = tail;
     if (avr_cab_consume(c, rec)) break;
   }
   g_dec.ring_tail = tail;
+#endif
   g_dec.cab_n = c.n; g_dec.cab_err = c.err;
 }
 #endif
@@ -305,7 +348,7 @@ AVR_DEC_INL void avr_ring_reserve(uint32_t head, uint32_t& tail_seen, uint32_t n
 #if defined(__CUDACC__)
   if (head + n - 1 - tail_seen >= AVR_RING - 1) {
     uint32_t t;
-    do { t = g_dec.ring_tail; } while (head + n - 1 - t >= AVR_RING - 1);
+    do { t = g_dec.ring_tail; } while (AVR_DIAG_WAIT(head + n - 1 - t >= AVR_RING - 1));
     tail_seen = t;
   }
 #else
@@ -553,6 +596,9 @@ AVR_DEC_FN int avr_dec_slice(const AvrDecSlice& ds, const uint8_t* payloads, avr
   const int rc = parser.run();
   *out_bins = g_dec.ring_head - head0;
   if (!g_dec.done) avr_ring_post(AVR_REC_ABORT, 0);            // release the encoder thread
+#if defined(AVR_ENC_BATCH)
+  while (g_dec.ring_head & (AVR_RING_BATCH - 1)) avr_ring_post(AVR_REC_NOP, 0);   // the encoder takes whole batches
+#endif
   return rc < 0 ? AVR_E_CORRUPT : !g_dec.done ? AVR_E_CORRUPT : g_dec.pos > ds.payload_len + 16 ? AVR_E_CORRUPT : AVR_OK;
 }
 

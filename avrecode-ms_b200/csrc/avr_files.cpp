@@ -6,6 +6,7 @@
 #include <string.h>
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <chrono>
@@ -161,6 +162,67 @@ bool to_buffer(Buf& v, avr_buffer* b) {          // hands the bytes over: no cop
 
 extern "C" void avr_buffer_free(avr_buffer* b) { if (b) { free(b->data); b->data = nullptr; b->size = 0; } }
 
+// ---- lanes -------------------------------------------------------------------------------------------------------
+// The file-level calls cut their input into sub-batches and run them on several LANES: a lane is a context (own stream,
+// events, device-block and pinned caches) driven by its own host thread.  One batch's NAL scan, staging copies, D2H and
+// container framing then overlap another batch's kernels, and the tail of one batch's serial kernels (device parse, pass D,
+// chains: each lasts as long as its longest slice / file) is filled by the other lane's work.  With several contexts
+// (avr_*_files_multi) the lanes also span GPUs: files share nothing (recode.cpp:1314,1597), so no data moves between them.
+static int env_int(const char* name, int dflt, int lo, int hi) {
+  const char* e = getenv(name);
+  if (!e || !*e) return dflt;
+  const int v = atoi(e);
+  return v < lo ? lo : v > hi ? hi : v;
+}
+// Measured on B200, 2048 clips (tools/e2e_sweep.py, profiles/r02_e2e_lanes.md): compress gains from two concurrent batches
+// (566 against 666 ms; more batches or lanes only add tails), the chain kernel does not (two concurrent launches of 1024
+// chains take 1000 ms where one launch of 2048 takes 680 ms), so decompress defaults to one lane and one batch per context.
+static int make_lanes(avr_context* const* ctxs, int nctx, int per_ctx, std::vector<avr_context*>* lanes) {
+  for (int k = 0; k < per_ctx; k++)            // lane k of every context before lane k + 1: batches are handed out in this order
+    for (int c = 0; c < nctx; c++) {
+      avr_context* l = avr_context_lane(ctxs[c], k);
+      if (!l) return AVR_E_CUDA;
+      lanes->push_back(l);
+    }
+  return AVR_OK;
+}
+// files -> nb sub-batches of similar weight: heaviest first onto the lightest batch (greedy LPT)
+static std::vector<std::vector<int>> lpt_batches(const std::vector<int>& ids, const std::vector<uint64_t>& weight, int nb) {
+  std::vector<std::vector<int>> out((size_t)nb);
+  std::vector<uint64_t> load((size_t)nb, 0);
+  std::vector<int> order(ids);
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return weight[a] > weight[b]; });
+  for (int f : order) {
+    size_t best = 0;
+    for (size_t k = 1; k < out.size(); k++) if (load[k] < load[best]) best = k;
+    out[best].push_back(f); load[best] += weight[f] + 1;
+  }
+  for (auto& b : out) std::sort(b.begin(), b.end());
+  out.erase(std::remove_if(out.begin(), out.end(), [](const std::vector<int>& b) { return b.empty(); }), out.end());
+  return out;
+}
+// runs job(batch index, lane context, host threads of the lane) for every batch; batches are pulled in order by one host
+// thread per lane.  Returns the first error (its message is re-raised on the calling thread: avr_last_error is thread-local).
+template <class Job>
+static int run_on_lanes(const std::vector<avr_context*>& lanes, int nbatches, int host_threads, Job&& job) {
+  const int nl = std::max(1, std::min((int)lanes.size(), nbatches));
+  const int lane_threads = std::max(1, host_threads / nl);
+  if (nl == 1) { for (int b = 0; b < nbatches; b++) { const int rc = job(b, lanes[0], host_threads); if (rc) return rc; } return AVR_OK; }
+  std::atomic<int> next(0), first_rc(AVR_OK);
+  std::string msg; std::mutex mu;
+  std::vector<std::thread> th;
+  for (int l = 0; l < nl; l++)
+    th.emplace_back([&, l] {
+      for (int b; first_rc.load() == AVR_OK && (b = next.fetch_add(1)) < nbatches;) {
+        const int rc = job(b, lanes[(size_t)l], lane_threads);
+        if (rc) { std::lock_guard<std::mutex> g(mu); if (first_rc.load() == AVR_OK) { first_rc = rc; msg = avr_last_error(); } }
+      }
+    });
+  for (auto& t : th) t.join();
+  if (first_rc.load() != AVR_OK) avr_set_error("%s", msg.c_str());
+  return first_rc.load();
+}
+
 // compressor::run (recode.cpp:1122-1132) for n files at once.
 // Phase 1 of avr_compress_files: batches whose CABAC parse runs on the GPU (avr_cbatch_create_files).
 // Marks done[f] for every file it produced a container for; the rest fall to the host recorder.
@@ -215,10 +277,9 @@ static int compress_device_parse(avr_context* ctx, const uint8_t* const* in, con
   return rc;
 }
 
-extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
-                                  avr_buffer* out, avr_timing* tacc) {
-  if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
-  if (n) memset(out, 0, (size_t)n * sizeof *out);          // output-only: all-null on every failure path
+static int compress_core(const std::vector<avr_context*>& lanes, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
+                         avr_buffer* out, avr_timing* tacc) {
+  avr_context* ctx = lanes[0];
   avr_timing tt; memset(&tt, 0, sizeof tt);
   const double t_call0 = now_ms();
   std::vector<Buf> containers((size_t)n);
@@ -226,14 +287,26 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
   int rc = AVR_OK;
   // AVR_HOST_PARSE=1 keeps the CABAC parse on the host cores (A/B measurement, bench.py)
   const char* hp = getenv("AVR_HOST_PARSE");
-  if (!(hp && hp[0] == '1')) {
-    // batches: at most AVR_MAX_BATCH_FILES files and 192 MB of input each (~8.4 coded symbols per input byte on High-profile
-    // streams, the launch limit is 2^31); a batch that still exceeds the limit is halved (AVR_E_OVERFLOW)
-    for (int i0 = 0; i0 < n && rc == AVR_OK;) {
-      std::vector<int> ids; size_t bytes = 0;
-      for (; i0 < n && ids.size() < AVR_MAX_BATCH_FILES && (ids.empty() || bytes + in_len[i0] <= (192u << 20)); i0++) { ids.push_back(i0); bytes += in_len[i0]; }
-      rc = compress_device_parse(ctx, in, in_len, ids, host_threads, containers, done, &tt);
-    }
+  if (!(hp && hp[0] == '1') && n > 0) {
+    // sub-batches: at most AVR_MAX_BATCH_FILES files and 160 MB of input each (~8.4 coded symbols per input byte on High-profile
+    // streams, the launch limit is 2^31); a batch that still exceeds the limit is halved (AVR_E_OVERFLOW).  One batch per lane
+    // unless the limits ask for more: every further batch adds the tail of its longest slice.
+    std::vector<int> ids((size_t)n); std::vector<uint64_t> w((size_t)n);
+    uint64_t bytes = 0;
+    for (int f = 0; f < n; f++) { ids[f] = f; w[f] = in_len[f]; bytes += in_len[f]; }
+    int nb = (int)lanes.size() * env_int("AVR_BATCHES_PER_LANE", 1, 1, 16);
+    nb = std::min(nb, std::max(1, n / 64));
+    nb = std::max(nb, (int)((bytes + (160u << 20) - 1) / (160u << 20)));
+    nb = std::max(nb, (n + AVR_MAX_BATCH_FILES - 1) / AVR_MAX_BATCH_FILES);
+    const std::vector<std::vector<int>> batches = lpt_batches(ids, w, nb);
+    std::mutex mu;
+    rc = run_on_lanes(lanes, (int)batches.size(), host_threads, [&](int b, avr_context* lane, int threads) {
+      avr_timing t; memset(&t, 0, sizeof t);
+      const int r = compress_device_parse(lane, in, in_len, batches[(size_t)b], threads, containers, done, &t);
+      std::lock_guard<std::mutex> g(mu);
+      add_timing(&tt, t);
+      return r;
+    });
     if (rc != AVR_OK) return rc;
   }
   // host recorder for what the device parse left (record capacity exceeded, syntax it rejects)
@@ -304,9 +377,23 @@ extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, co
   cleanup();
   avr_trace("c: to_buffer");
   if (nomem) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return AVR_E_NOMEM; }
-  tt.host_ms = now_ms() - t_call0 - (tt.h2d_ms + tt.parse_ms + tt.kernel_ms + tt.d2h_ms);   // everything not on the device clock
+  // with several lanes the device times of concurrent batches add up beyond the wall time: host_ms is then what is left, not below 0
+  tt.host_ms = std::max(0.0, now_ms() - t_call0 - (tt.h2d_ms + tt.parse_ms + tt.kernel_ms + tt.d2h_ms));
   if (tacc) *tacc = tt;
   return AVR_OK;
+}
+extern "C" int avr_compress_files_multi(avr_context* const* ctxs, int nctx, const uint8_t* const* in, const size_t* in_len, int n,
+                                        int host_threads, avr_buffer* out, avr_timing* tacc) {
+  if (!ctxs || nctx <= 0 || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
+  for (int c = 0; c < nctx; c++) if (!ctxs[c]) return AVR_E_ARG;
+  if (n) memset(out, 0, (size_t)n * sizeof *out);          // output-only: all-null on every failure path
+  std::vector<avr_context*> lanes;
+  if (make_lanes(ctxs, nctx, env_int("AVR_LANES", 2, 1, 8), &lanes)) return AVR_E_CUDA;
+  return compress_core(lanes, in, in_len, n, host_threads, out, tacc);
+}
+extern "C" int avr_compress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
+                                  avr_buffer* out, avr_timing* tacc) {
+  return avr_compress_files_multi(&ctx, 1, in, in_len, n, host_threads, out, tacc);
 }
 
 // decompressor::run (recode.cpp:1345-1364) for n containers at once.
@@ -320,10 +407,8 @@ struct DFile {
 };
 }  // namespace
 
-extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
-                                    avr_buffer* out, avr_timing* tacc) {
-  if (!ctx || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
-  if (n) memset(out, 0, (size_t)n * sizeof *out);          // output-only: all-null on every failure path
+static int decompress_core(const std::vector<avr_context*>& lanes, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
+                           avr_buffer* out, avr_timing* tacc) {
   avr_timing tt; memset(&tt, 0, sizeof tt);
   const double t_call0 = now_ms();
   avr_trace(nullptr);
@@ -428,43 +513,65 @@ extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, 
   };
   std::vector<char> assembled((size_t)n, 0);
   int rc = AVR_OK;
-  int f0 = 0;
-  while (f0 < n && rc == AVR_OK) {
-    std::vector<avr_dslice> sl; std::vector<uint32_t> per; std::vector<int> ids;
+  {
+    // sub-batches over the lanes: every chain kernel lasts as long as its longest file, and a chain runs the faster the fewer
+    // chains share its SM, so the files are spread by payload bytes (greedy LPT) and at most AVR_MAX_BATCH_FILES go into one launch
+    std::vector<int> ids; std::vector<uint64_t> w((size_t)n, 0);
     uint64_t bytes = 0;
-    int f = f0;
-    for (; f < n && ids.size() < 4096; f++) {
+    for (int f = 0; f < n; f++) {
       if (files[f].slices.empty()) continue;
-      uint64_t fb = 0; for (auto& s : files[f].slices) fb += s.payload_len + s.size;
-      if (!ids.empty() && bytes + fb > (8ull << 30)) break;
-      ids.push_back(f); per.push_back((uint32_t)files[f].slices.size()); bytes += fb;
-      sl.insert(sl.end(), files[f].slices.begin(), files[f].slices.end());
+      for (auto& sl : files[f].slices) w[f] += sl.payload_len + sl.size;
+      ids.push_back(f); bytes += w[f];
     }
-    f0 = f;
-    if (ids.empty()) continue;
-    avr_dbatch* b = nullptr;
-    avr_trace("d: batch lists");
-    rc = avr_dbatch_create(ctx, sl.data(), per.data(), (int)ids.size(), &b);
-    avr_trace(nullptr);
-    if (rc == AVR_OK) rc = avr_dbatch_run(b);
-    avr_trace("d: run");
-    if (rc == AVR_OK) rc = avr_dbatch_fetch(b);
-    avr_trace("d: fetch");
-    if (rc == AVR_OK) {
-      avr_timing t; avr_dbatch_timing(b, &t); add_timing(&tt, t);
-      std::vector<uint32_t> first(ids.size(), 0);
-      for (size_t k = 1; k < ids.size(); k++) first[k] = first[k - 1] + per[k - 1];
-      parallel_for((int)ids.size(), host_threads, [&](int k) { assemble(ids[k], b, first[k]); assembled[ids[k]] = 1; });
-      avr_trace("d: assemble batch");
+    int nb = (int)lanes.size() * env_int("AVR_DBATCHES_PER_LANE", 1, 1, 16);
+    nb = std::min(nb, std::max(1, (int)ids.size() / 64));
+    nb = std::max(nb, (int)((bytes + (8ull << 30) - 1) / (8ull << 30)));
+    nb = std::max(nb, ((int)ids.size() + AVR_MAX_BATCH_FILES - 1) / AVR_MAX_BATCH_FILES);
+    const std::vector<std::vector<int>> batches = ids.empty() ? std::vector<std::vector<int>>() : lpt_batches(ids, w, nb);
+    {
+      int inflight = 0;                                         // chains resident at once: the first batch of every lane
+      for (size_t b = 0; b < batches.size() && b < lanes.size(); b++) inflight += (int)batches[b].size();
+      avr_set_chain_concurrency_hint(inflight);
     }
-    avr_dbatch_destroy(b);
-    avr_trace("d: destroy");
+    std::mutex mu;
+    rc = run_on_lanes(lanes, (int)batches.size(), host_threads, [&](int bi, avr_context* lane, int threads) {
+      const std::vector<int>& bids = batches[(size_t)bi];
+      std::vector<avr_dslice> sl; std::vector<uint32_t> per;
+      for (int f : bids) { per.push_back((uint32_t)files[f].slices.size()); sl.insert(sl.end(), files[f].slices.begin(), files[f].slices.end()); }
+      avr_dbatch* b = nullptr;
+      int r = avr_dbatch_create(lane, sl.data(), per.data(), (int)bids.size(), &b);
+      if (r == AVR_OK) r = avr_dbatch_run(b);
+      if (r == AVR_OK) r = avr_dbatch_fetch(b);
+      if (r == AVR_OK) {
+        avr_timing t; avr_dbatch_timing(b, &t);
+        { std::lock_guard<std::mutex> g(mu); add_timing(&tt, t); }
+        std::vector<uint32_t> first(bids.size(), 0);
+        for (size_t k = 1; k < bids.size(); k++) first[k] = first[k - 1] + per[k - 1];
+        parallel_for((int)bids.size(), threads, [&](int k) { assemble(bids[(size_t)k], b, first[(size_t)k]); assembled[bids[(size_t)k]] = 1; });
+      }
+      avr_dbatch_destroy(b);
+      return r;
+    });
+    avr_set_chain_concurrency_hint(0);
   }
   if (rc != AVR_OK) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return rc; }
   parallel_for(n, host_threads, [&](int f) { if (!assembled[f]) assemble(f, nullptr, 0); });   // files without coded blocks: literals only
   if (nomem) { for (int f = 0; f < n; f++) { free(out[f].data); out[f].data = nullptr; out[f].size = 0; } return AVR_E_NOMEM; }
   avr_trace("d: assemble");
-  tt.host_ms = now_ms() - t_call0 - (tt.h2d_ms + tt.kernel_ms + tt.d2h_ms);
+  tt.host_ms = std::max(0.0, now_ms() - t_call0 - (tt.h2d_ms + tt.kernel_ms + tt.d2h_ms));
   if (tacc) *tacc = tt;
   return AVR_OK;
+}
+extern "C" int avr_decompress_files_multi(avr_context* const* ctxs, int nctx, const uint8_t* const* in, const size_t* in_len, int n,
+                                          int host_threads, avr_buffer* out, avr_timing* tacc) {
+  if (!ctxs || nctx <= 0 || !in || !in_len || n < 0 || !out) return AVR_E_ARG;
+  for (int c = 0; c < nctx; c++) if (!ctxs[c]) return AVR_E_ARG;
+  if (n) memset(out, 0, (size_t)n * sizeof *out);          // output-only: all-null on every failure path
+  std::vector<avr_context*> lanes;
+  if (make_lanes(ctxs, nctx, env_int("AVR_DLANES", 1, 1, 8), &lanes)) return AVR_E_CUDA;
+  return decompress_core(lanes, in, in_len, n, host_threads, out, tacc);
+}
+extern "C" int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
+                                    avr_buffer* out, avr_timing* tacc) {
+  return avr_decompress_files_multi(&ctx, 1, in, in_len, n, host_threads, out, tacc);
 }

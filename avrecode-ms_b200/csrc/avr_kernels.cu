@@ -32,6 +32,13 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
 // steps between slices: zeroing the picture stores on a flip, CABAC state initialisation, staging
 // the per-bin tables and the default-key estimators in shared memory.
 #define AVR_DEC_THREADS 64
+#if defined(AVR_SWAP_WARPS)
+#define AVR_CHAIN_TID 32
+#define AVR_ENC_TID 0
+#else
+#define AVR_CHAIN_TID 0
+#define AVR_ENC_TID 32
+#endif
 __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     const AvrFileDesc* fds, int nfiles, const AvrDecSlice* slices, const uint8_t* payloads, uint16_t* est_pool,
     uint8_t* store_pool, avr::MbInfo* row_pool, const AvrTables* tab, uint8_t* out, uint32_t* out_len, uint32_t* out_bins,
@@ -70,10 +77,10 @@ __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     avr_cabac_init_states(g_dec.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, tid, AVR_DEC_THREADS);
     __syncthreads();
     int rc = 0;
-    if (tid == 0) rc = avr_dec_slice(ds, payloads, row_pool + fd.mb_base, ++uid, &out_bins[g]);
-    else if (tid == 32) avr_cab_encoder_thread(out + ds.out_off, ds.out_cap);
+    if (tid == AVR_CHAIN_TID) rc = avr_dec_slice(ds, payloads, row_pool + fd.mb_base, ++uid, &out_bins[g]);
+    else if (tid == AVR_ENC_TID) avr_cab_encoder_thread(out + ds.out_off, ds.out_cap);
     __syncthreads();
-    if (tid == 0) {
+    if (tid == AVR_CHAIN_TID) {
       if (!rc) rc = g_dec.cab_err;
       out_len[g] = g_dec.cab_n; status[g] = rc;
       if (rc) s_failed = 1;
@@ -164,6 +171,10 @@ int avr_launch_compress_chain(const AvrDevBatch& b, cudaStream_t st) {
   return (int)cudaGetLastError();
 }
 
+#include <atomic>
+static std::atomic<int> g_chain_hint(0);
+void avr_set_chain_concurrency_hint(int files) { g_chain_hint = files; }
+
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
   if (b.nfiles == 0) return 0;
   {
@@ -177,7 +188,8 @@ int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
     int pct = -1;
     if (const char* e = getenv("AVR_DEC_CARVEOUT")) pct = atoi(e);
     else if (cudaFuncGetAttributes(&fa, avr_k_decompress_chain) == cudaSuccess) {
-      const int per_sm = (b.nfiles + sms - 1) / sms;
+      const int hint = g_chain_hint.load(), chains = hint > b.nfiles ? hint : b.nfiles;   // launches of other lanes share the SMs
+      const int per_sm = (chains + sms - 1) / sms;
       const size_t need = (size_t)per_sm * (fa.sharedSizeBytes + 1024);      // + the per-block reservation
       pct = (int)((need * 100 + 233471) / 233472);
       if (pct > 100) pct = 100;

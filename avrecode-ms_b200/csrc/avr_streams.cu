@@ -265,3 +265,52 @@ extern "C" int avr_streams_encode_static(avr_context* ctx, const uint8_t* d_bits
 done:
   return rc;
 }
+
+// ---- avr_measure_recurrence_floor: what ONE thread can do per bin when nothing but the decoder's recurrence is left ----
+// low/range -> r1 = (range / total) * pos -> symbol = low >= range - r1 -> low/range (arithmetic_code.h:232-248 with the
+// exact multiply-high division of avr_div_tab.h), a CONSTANT estimator (pos 40 of total 81), digits from a register
+// generator: no estimator load/update, no context selection, no CABAC re-encode, no ring.  The chain kernel's
+// cycles-per-bin are reported against this number (bench.py roofline.serial_chain); it replaces a planning constant.
+__global__ void __launch_bounds__(32) avr_k_recurrence_floor(uint32_t steps, uint64_t m, uint32_t sh, uint32_t pos, uint64_t seed,
+                                                             unsigned long long* out) {
+  if (threadIdx.x != 0) return;
+  uint64_t low = seed >> 1, range = 1ull << 63, x = seed;
+  uint32_t ones = 0;
+  const long long t0 = clock64();
+  for (uint32_t i = 0; i < steps; i++) {
+    const uint64_t r1 = (__umul64hi(range, m) >> sh) * (uint64_t)pos;
+    const uint64_t r0 = range - r1;
+    const uint32_t sym = low >= r0;
+    low -= sym ? r0 : 0ull;
+    range = sym ? r1 : r0;
+    ones += sym;
+    if (range < (1ull << 51)) {
+      while (range < (1ull << 55)) {
+        x = x * 6364136223846793005ull + 1442695040888963407ull;          // the next digit (off the recurrence: does not depend on low/range)
+        low = (low << 8) + (x >> 56);
+        range <<= 8;
+      }
+    }
+  }
+  const long long t1 = clock64();
+  out[0] = (unsigned long long)(t1 - t0); out[1] = ones; out[2] = low ^ range;
+}
+extern "C" int avr_measure_recurrence_floor(avr_context* ctx, uint32_t steps, double* cycles_per_bin) {
+  if (!ctx || !cycles_per_bin || steps == 0) { avr_set_error("recurrence_floor: bad argument"); return AVR_E_ARG; }
+  int rc = AVR_OK;
+  if (cudaSetDevice(avr_context_device(ctx)) != cudaSuccess) { avr_set_error("recurrence_floor: cudaSetDevice failed"); return AVR_E_CUDA; }
+  cudaStream_t st = (cudaStream_t)avr_context_stream(ctx);
+  static const AvrDivTab dt = AVR_DIV_TAB_INIT;
+  unsigned long long* d_out = nullptr; unsigned long long h[3] = {0, 0, 0};
+  CU(cudaMalloc(&d_out, sizeof h));
+  for (int rep = 0; rep < 2; rep++) {                                        // the first launch loads the module
+    avr_k_recurrence_floor<<<1, 32, 0, st>>>(steps, dt.m[81], dt.s[81], 40, 0x9E3779B97F4A7C15ull, d_out);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(h, d_out, sizeof h, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  *cycles_per_bin = (double)h[0] / steps;
+done:
+  cudaFree(d_out);
+  return rc;
+}

@@ -3,6 +3,8 @@
 //   recode test <directory>                                     roundtrip of every regular file, <dir>/output/metrics.csv
 // plus the batch form the GPU path exists for:
 //   recode compress-batch|roundtrip-batch <file>...            outputs <file>.avrec / report only
+//   --gpus N (anywhere on the line, or RECODE_GPUS=N)          files are spread over the first N GPUs of the box, greedy
+//                                                              longest-first (avr_*_files_multi); same bytes out for any N
 // All entropy coding runs on the GPU through include/avrecode_b200.h; there is no CPU path.
 #include <chrono>
 #include <cstdio>
@@ -35,6 +37,16 @@ static int fail(const std::string& what) {
   fprintf(stderr, "Exception (avr_error): %s\n", what.c_str());   // shape of recode.cpp:1672-1675
   return 1;
 }
+// one context per GPU asked for (--gpus N); fewer when the box has fewer
+static bool open_contexts(int want, std::vector<avr_context*>* ctxs) {
+  for (int d = 0; d < want; d++) {
+    avr_context* c = nullptr;
+    if (avr_context_create(d, &c) != AVR_OK) { if (d == 0) return false; break; }
+    ctxs->push_back(c);
+  }
+  return true;
+}
+static void close_contexts(std::vector<avr_context*>& ctxs) { for (auto c : ctxs) avr_context_destroy(c); ctxs.clear(); }
 static double now_ms() {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -43,7 +55,7 @@ static double now_ms() {
 // <dir>/output/, results in <dir>/output/metrics.csv with the reference's columns (test.cpp:32) plus Bins and
 // Gbins/s.  The files go through the GPU as ONE batch, so the per-file times are the batch times apportioned by file
 // size; Duration / Video stream / Frames per second come from libavformat's dump in the reference and are "n/a" here.
-static int run_test(const std::string& dir, int threads) {
+static int run_test(const std::string& dir, int threads, int gpus) {
   namespace fs = std::filesystem;
   std::vector<std::string> names;
   std::error_code ec;
@@ -54,17 +66,17 @@ static int run_test(const std::string& dir, int threads) {
   const int n = (int)names.size();
   std::vector<std::vector<uint8_t>> data((size_t)n);
   for (int i = 0; i < n; i++) if (!read_file(names[i], &data[i])) return fail("Failed to open file: " + names[i]);
-  avr_context* ctx = nullptr;
-  if (avr_context_create(0, &ctx) != AVR_OK) return fail(avr_last_error());
+  std::vector<avr_context*> ctxs;
+  if (!open_contexts(gpus, &ctxs)) return fail(avr_last_error());
   std::vector<const uint8_t*> in, cin; std::vector<size_t> len, clen;
   for (auto& d : data) { in.push_back(d.data()); len.push_back(d.size()); }
   std::vector<avr_buffer> comp((size_t)n), dec((size_t)n);
   avr_timing tc, td;
   const double t0 = now_ms();
-  if (avr_compress_files(ctx, in.data(), len.data(), n, threads, comp.data(), &tc) != AVR_OK) return fail(avr_last_error());
+  if (avr_compress_files_multi(ctxs.data(), (int)ctxs.size(), in.data(), len.data(), n, threads, comp.data(), &tc) != AVR_OK) return fail(avr_last_error());
   const double t1 = now_ms();
   for (auto& c : comp) { cin.push_back(c.data); clen.push_back(c.size); }
-  if (avr_decompress_files(ctx, cin.data(), clen.data(), n, threads, dec.data(), &td) != AVR_OK) return fail(avr_last_error());
+  if (avr_decompress_files_multi(ctxs.data(), (int)ctxs.size(), cin.data(), clen.data(), n, threads, dec.data(), &td) != AVR_OK) return fail(avr_last_error());
   const double t2 = now_ms();
   double total = 0;
   for (auto& d : data) total += (double)d.size();
@@ -93,11 +105,22 @@ static int run_test(const std::string& dir, int threads) {
   printf("%d files, %.1f MB: compress %.1f MB/s, decompress %.1f MB/s, %.2f Gbins/s roundtrip\n", n, total / 1e6, total / 1e3 / (t1 - t0),
          total / 1e3 / (t2 - t1), tc.bins / 1e6 / (t2 - t0));
   if (failed) printf("Compress-decompress roundtrip failed on %d / %d files\n", failed, n);
-  avr_context_destroy(ctx);
+  close_contexts(ctxs);
   return failed ? 1 : 0;
 }
 
 int main(int argc, char** argv) {
+  int gpus = 1;
+  if (const char* e = getenv("RECODE_GPUS")) gpus = atoi(e);
+  {                                                  // --gpus N is ours, not the reference's: taken off the line before its parse
+    int w = 1;
+    for (int i = 1; i < argc; i++) {
+      if (!strcmp(argv[i], "--gpus") && i + 1 < argc) { gpus = atoi(argv[++i]); continue; }
+      argv[w++] = argv[i];
+    }
+    argc = w;
+  }
+  if (gpus < 1) gpus = 1;
   if (argc < 3) {
     fprintf(stderr, "Usage: %s [compress|decompress|roundtrip|test] <input> [output]\n", argv[0]);
     return 1;
@@ -105,7 +128,7 @@ int main(int argc, char** argv) {
   std::string cmd = argv[1];
   int threads = (int)std::thread::hardware_concurrency();
   if (threads < 1) threads = 1;
-  if (cmd == "test") return run_test(argv[2], threads);
+  if (cmd == "test") return run_test(argv[2], threads, gpus);
   bool batch = cmd == "compress-batch" || cmd == "roundtrip-batch";
   if (!batch && cmd != "compress" && cmd != "decompress" && cmd != "roundtrip") {
     fprintf(stderr, "Unknown command: %s\n", cmd.c_str());
@@ -117,21 +140,22 @@ int main(int argc, char** argv) {
   std::vector<std::vector<uint8_t>> data(names.size());
   for (size_t i = 0; i < names.size(); i++)
     if (!read_file(names[i], &data[i])) return fail("Failed to open file: " + names[i]);
-  avr_context* ctx = nullptr;
-  if (avr_context_create(0, &ctx) != AVR_OK) return fail(avr_last_error());
+  std::vector<avr_context*> ctxs;
+  if (!open_contexts(gpus, &ctxs)) return fail(avr_last_error());
+  const int nctx = (int)ctxs.size();
   std::vector<const uint8_t*> in; std::vector<size_t> len;
   for (auto& d : data) { in.push_back(d.data()); len.push_back(d.size()); }
   const int n = (int)names.size();
   std::vector<avr_buffer> comp((size_t)n), dec((size_t)n);
   int rc = 0;
   if (cmd == "decompress") {
-    if (avr_decompress_files(ctx, in.data(), len.data(), 1, threads, dec.data(), nullptr) != AVR_OK) return fail(avr_last_error());
+    if (avr_decompress_files_multi(ctxs.data(), nctx, in.data(), len.data(), 1, threads, dec.data(), nullptr) != AVR_OK) return fail(avr_last_error());
     if (!write_out(outname, dec[0].data, dec[0].size)) return fail("write failed");
     return 0;
   }
   avr_timing tc, td;
   double t0 = now_ms();
-  if (avr_compress_files(ctx, in.data(), len.data(), n, threads, comp.data(), &tc) != AVR_OK) return fail(avr_last_error());
+  if (avr_compress_files_multi(ctxs.data(), nctx, in.data(), len.data(), n, threads, comp.data(), &tc) != AVR_OK) return fail(avr_last_error());
   double t1 = now_ms();
   if (cmd == "compress") { if (!write_out(outname, comp[0].data, comp[0].size)) return fail("write failed"); return 0; }
   if (cmd == "compress-batch") {
@@ -140,7 +164,7 @@ int main(int argc, char** argv) {
   }
   std::vector<const uint8_t*> cin; std::vector<size_t> clen;
   for (auto& c : comp) { cin.push_back(c.data); clen.push_back(c.size); }
-  if (avr_decompress_files(ctx, cin.data(), clen.data(), n, threads, dec.data(), &td) != AVR_OK) return fail(avr_last_error());
+  if (avr_decompress_files_multi(ctxs.data(), nctx, cin.data(), clen.data(), n, threads, dec.data(), &td) != AVR_OK) return fail(avr_last_error());
   double t2 = now_ms();
   size_t orig = 0, csz = 0;
   for (int i = 0; i < n; i++) {
@@ -153,6 +177,6 @@ int main(int argc, char** argv) {
   printf(" compression ratio: %.2f%%\n", orig ? 100.0 * csz / orig : 0.0);
   printf(" compress: %.1f ms (%.1f MB/s)  decompress: %.1f ms (%.1f MB/s)  bins: %llu\n", t1 - t0, orig / 1e3 / (t1 - t0),
          t2 - t1, orig / 1e3 / (t2 - t1), (unsigned long long)tc.bins);
-  avr_context_destroy(ctx);
+  close_contexts(ctxs);
   return rc;
 }

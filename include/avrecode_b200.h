@@ -142,7 +142,17 @@ int avr_compress_files(avr_context* ctx, const uint8_t* const* in, const size_t*
                        avr_buffer* out, avr_timing* t);
 int avr_decompress_files(avr_context* ctx, const uint8_t* const* in, const size_t* in_len, int n, int host_threads,
                          avr_buffer* out, avr_timing* t);
+/* `out` is output-only: zeroed on entry, all-null when the call fails.  Internally the files are cut into sub-batches that run on
+ * lanes (stream + host thread each; compress AVR_LANES, default 2; decompress AVR_DLANES, default 1) so that one batch's copies,
+ * host framing and kernel tails overlap another batch's kernels. */
 void avr_buffer_free(avr_buffer* b);
+/* The same over several contexts, normally one per GPU of the box: sub-batches are spread over the contexts by
+ * greedy longest-first on bytes; files share nothing (recode.cpp:1314,1597), so nothing moves between GPUs.  The outputs do
+ * not depend on the number of contexts.  `recode compress|decompress|roundtrip --gpus N` uses these. */
+int avr_compress_files_multi(avr_context* const* ctxs, int nctx, const uint8_t* const* in, const size_t* in_len, int n,
+                             int host_threads, avr_buffer* out, avr_timing* t);
+int avr_decompress_files_multi(avr_context* const* ctxs, int nctx, const uint8_t* const* in, const size_t* in_len, int n,
+                               int host_threads, avr_buffer* out, avr_timing* t);
 
 /* ---- streams: the reference's coder test on S independent bin streams (test/arithmetic_code.cpp:93-110) ---- */
 /* bits: nstreams * nbins bytes, stream-major, one byte per bin (zero / non-zero).  digit_bits selects
@@ -156,6 +166,10 @@ int avr_streams_encode(avr_context* ctx, const uint8_t* bits, uint32_t nstreams,
                        avr_buffer* coded, uint64_t* coded_off, avr_timing* t);
 int avr_streams_decode(avr_context* ctx, const uint8_t* coded, const uint64_t* coded_off, uint32_t nstreams, uint32_t nbins,
                        int digit_bits, int model, uint8_t* bits_out, avr_timing* t);
+
+/* ---- measurement aid: SM cycles per bin of the range decoder's bare recurrence on one thread (arithmetic_code.h:232-248 with
+ * a constant estimator, nothing else); the denominator bench.py reports the chain kernel's cycles per bin against. */
+int avr_measure_recurrence_floor(avr_context* ctx, uint32_t steps, double* cycles_per_bin);
 
 /* ---- streams, no-allocation variant ------------------------------------------------------------------------ */
 /* No counterpart in the reference: added for callers that cannot call

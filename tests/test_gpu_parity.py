@@ -300,3 +300,36 @@ def test_single_file_batches_without_coded_slices(ctx, tmpdir_path, kind):
     assert open(dst, "rb").read() == comp[0]
     assert run([exe, "decompress", dst, rt])[0] == 0
     assert open(rt, "rb").read() == blob
+
+
+def test_lanes_and_multi_context_give_the_same_containers(ctx, tmpdir_path, monkeypatch):
+    """avr_*_files cut their input into sub-batches over several lanes (AVR_LANES) and avr_*_files_multi over several contexts
+    (one per GPU): the containers and the restored files must not depend on either"""
+    import avr_ctypes as A
+    import torch
+    datas = [gen_clip(os.path.join(tmpdir_path, f"m{i}.h264"), seed=300 + i, mb_w=6 + i % 5, mb_h=4 + i % 3, frames=2 + i % 3,
+                      slices_per_frame=1 + i % 2, transform_8x8=i & 1) for i in range(160)]
+    datas[7] = b"not a stream"                      # a literal-only file in the middle of a batch
+    monkeypatch.setenv("AVR_LANES", "1")
+    want, _ = A.compress_files(ctx, datas)
+    for lanes, bpl in (("2", "2"), ("3", "1")):
+        monkeypatch.setenv("AVR_LANES", lanes)
+        monkeypatch.setenv("AVR_DLANES", lanes)
+        monkeypatch.setenv("AVR_BATCHES_PER_LANE", bpl)
+        monkeypatch.setenv("AVR_DBATCHES_PER_LANE", bpl)
+        got, t = A.compress_files(ctx, datas)
+        assert got == want
+        back, _ = A.decompress_files(ctx, got)
+        assert back == datas
+    other = A.Context(1 if torch.cuda.device_count() > 1 else 0)
+    try:
+        got, _ = A.compress_files_multi([ctx, other], datas)
+        assert got == want
+        back, _ = A.decompress_files_multi([ctx, other], got)
+        assert back == datas
+    finally:
+        other.close()
+    # the CLI form
+    exe = os.path.join(ROOT, "avrecode-ms_b200", "bin", "recode")
+    paths = [os.path.join(tmpdir_path, f"m{i}.h264") for i in range(0, 160, 2) if i != 7]
+    assert run([exe, "roundtrip-batch", "--gpus", "2"] + paths)[0] == 0
