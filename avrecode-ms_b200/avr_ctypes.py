@@ -108,6 +108,15 @@ def lib():
                                          C.c_char_p, C.POINTER(Timing)]
         L.avr_streams_encode_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                                 C.c_uint64, C.c_void_p]
+        L.avr_rec_frame_spec.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.avr_rec_slice_begin.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_uint32, C.POINTER(SliceParams)]
+        L.avr_rec_slice_end.argtypes = [C.c_void_p]
+        L.avr_rec_mb_xy.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.avr_rec_begin_sub_mb.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.avr_rec_end_sub_mb.argtypes = [C.c_void_p]
+        L.avr_rec_begin_coding_type.argtypes = [C.c_void_p, C.c_int]
+        L.avr_rec_end_coding_type.argtypes = [C.c_void_p, C.c_int]
+        L.avr_rec_bin.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.avr_measure_recurrence_floor.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_double)]
         _lib = L
     return _lib
@@ -161,6 +170,59 @@ class Record:
         if self.h:
             lib().avr_record_free(self.h)
             self.h = C.c_void_p()
+
+
+class HookRecord(Record):
+    """A record filled through the AVCodecHooks-shaped sinks (avr_rec_*), the way a libavcodec-hooks Driver fills it
+    (oracle/gpu_driver.cpp is the compiled one).  `events` = lines of the hook trace `oracle/_ref/ref_harness trace` prints from the
+    reference's own av_decoder<> (format in oracle/ref_harness.cpp)."""
+
+    PIP_SIGNIFICANCE_MAP = 2            # coding_hooks.h:10-22
+
+    def __init__(self, events):
+        L = lib()
+        self.h = C.c_void_p(L.avr_record_new())
+        self.rc = 0
+        fnum, last_frame, open_slice, w, h = 0, None, False, 0, 0
+        for ln in events:
+            t = ln.split()
+            if not t:
+                continue
+            k = t[0]
+            if k == "c":
+                L.avr_rec_bin(self.h, int(t[1]), int(t[2]))
+            elif k == "b":
+                L.avr_rec_bin(self.h, 1024, int(t[1]))
+            elif k == "t":
+                L.avr_rec_bin(self.h, 1025, int(t[1]))
+            elif k == "M":
+                L.avr_rec_mb_xy(self.h, int(t[1]), int(t[2]))
+            elif k == "B":
+                L.avr_rec_begin_sub_mb(self.h, *[int(x) for x in t[1:6]])
+            elif k == "[":
+                L.avr_rec_begin_coding_type(self.h, self.PIP_SIGNIFICANCE_MAP)
+            elif k == "]":
+                L.avr_rec_end_coding_type(self.h, self.PIP_SIGNIFICANCE_MAP)
+                L.avr_rec_end_sub_mb(self.h)
+            elif k == "F":                      # the model's cur_frame after ModelHooks::frame_spec: a flip shows as a new value
+                cur = (int(t[1]), int(t[2]), int(t[3]))
+                if cur != last_frame:
+                    last_frame, fnum = cur, fnum + 1
+                    w, h = cur[1], cur[2]
+                    L.avr_rec_frame_spec(self.h, fnum, w, h)
+            elif k == "S":                      # CABACCodingHooks::init_decoder + the Driver's block-finder decision
+                if open_slice:
+                    L.avr_rec_slice_end(self.h)
+                sp = SliceParams()
+                sp.mb_w, sp.mb_h = w, h
+                off = int(t[2])
+                L.avr_rec_slice_begin(self.h, 1 if off >= 0 else 0, max(off, 0), int(t[1]), C.byref(sp))
+                open_slice = True
+        if open_slice:
+            L.avr_rec_slice_end(self.h)
+        c = (C.c_uint64 * 6)()
+        L.avr_record_counts(self.h, c)
+        self.bins, self.blocks, self.slices, self.nspans, self.pictures, self.out_of_domain = [int(x) for x in c]
 
 
 class CBatch:

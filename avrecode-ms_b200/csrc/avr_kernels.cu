@@ -192,7 +192,9 @@ int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
       const int per_sm = (chains + sms - 1) / sms;
       const size_t need = (size_t)per_sm * (fa.sharedSizeBytes + 1024);      // + the per-block reservation
       pct = (int)((need * 100 + 233471) / 233472);
-      if (pct > 100) pct = 100;
+      // more than half of the array as shared memory costs more in L1 misses of the estimator cells than the extra resident
+      // chains bring: 2048-clip corpus, 606 ms at 70 % (all chains resident), 594 at 60 %, 588 at 50 % (profiles/r02_summary.md)
+      if (pct > 50) pct = 50;
     }
     if (pct >= 0) cudaFuncSetAttribute(avr_k_decompress_chain, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   }

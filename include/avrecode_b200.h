@@ -89,8 +89,12 @@ void* avr_context_stream(avr_context* ctx);               /* cudaStream_t the li
 avr_record* avr_record_new(void);
 void avr_record_free(avr_record* r);
 void avr_rec_frame_spec(avr_record* r, int frame_num, int mb_width, int mb_height);        /* ModelHooks::frame_spec */
+/* CABACCodingHooks::init_decoder.  coded / payload_off / size are the Driver's block-finder decision (recode.cpp:1282-1304: where
+ * the slice's CABAC bytes sit in the original file, or coded = 0 for a slice that stays literal / skip_coded); init_decoder's own
+ * arguments give buf and size.  sp is stored for avr_record_span only: the compress path never reads it (decompress derives it from
+ * the container's literal header bytes), so a hook Driver passes the picture size and zeros (oracle/gpu_driver.cpp does). */
 void avr_rec_slice_begin(avr_record* r, int coded, uint64_t payload_off, uint32_t size,
-                         const avr_slice_params* sp);                                      /* CABACCodingHooks::init_decoder */
+                         const avr_slice_params* sp);
 void avr_rec_slice_end(avr_record* r);
 void avr_rec_mb_xy(avr_record* r, int x, int y);                                           /* ModelHooks::mb_xy */
 void avr_rec_begin_sub_mb(avr_record* r, int cat, int scan8index, int max_coeff, int is_dc, int chroma422);

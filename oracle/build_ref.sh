@@ -11,6 +11,7 @@
 #   2. recode.cpp + test.cpp compiled -O2 -DNDEBUG (no ASan) against oracle/shim/recode.pb.h.
 #   3. test/arithmetic_code.cpp as-is.
 #   4. oracle/ref_harness.cpp (includes reference recode.cpp; drives its own classes).
+#   5. oracle/gpu_driver.cpp (includes reference recode.cpp; its hooks feed include/avrecode_b200.h, links the product .so).
 set -euo pipefail
 HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${AVR_REFERENCE:-/root/reference}"
@@ -45,5 +46,11 @@ $CXX "$SCRATCH/recode.o" "$SCRATCH/test.o" -o "$OUT/recode" $LIBS
 $CXX -std=c++17 -O2 -w $INC "$REF/test/arithmetic_code.cpp" -o "$OUT/arith_test" $LIBS
 if [ -f "$HERE/ref_harness.cpp" ]; then
   $CXX $FLAGS $INC -DAVR_REF_DIR="\"$REF\"" "$HERE/ref_harness.cpp" "$SCRATCH/test.o" -o "$OUT/ref_harness" $LIBS
+fi
+# oracle/gpu_driver.cpp: the reference's av_decoder<> + hooks driving the C ABI's recorder sinks and the GPU (lower-boundary test)
+PKGDIR="$HERE/../avrecode-ms_b200"
+if [ -f "$HERE/gpu_driver.cpp" ] && [ -f "$PKGDIR/libavrecode_b200.so" ]; then
+  $CXX $FLAGS $INC "$HERE/gpu_driver.cpp" "$SCRATCH/test.o" -o "$OUT/gpu_driver" $LIBS -L"$PKGDIR" -lavrecode_b200 \
+    -Wl,-rpath,'$ORIGIN/../../avrecode-ms_b200'
 fi
 echo "built: $(ls "$OUT")"
