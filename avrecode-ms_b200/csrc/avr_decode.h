@@ -592,8 +592,9 @@ AVR_DEC_FN int avr_dec_slice(const AvrDecSlice& ds, const uint8_t* payloads, avr
   g_dec.done = 0; g_dec.mb_addr = 0;
   const uint32_t head0 = g_dec.ring_head;                      // every bin posts exactly one record
   AvrDecPolicy io;
-  avr::SliceParser<AvrDecPolicy> parser(io, ds.sp, row, uid);
-  const int rc = parser.run();
+  int rc;
+  if (ds.sp.slice_type == avr::SLICE_B) { avr::SliceParser<AvrDecPolicy, true> parser(io, ds.sp, row, uid); rc = parser.run(); }
+  else { avr::SliceParser<AvrDecPolicy, false> parser(io, ds.sp, row, uid); rc = parser.run(); }
   *out_bins = g_dec.ring_head - head0;
   if (!g_dec.done) avr_ring_post(AVR_REC_ABORT, 0);            // release the encoder thread
 #if defined(AVR_ENC_BATCH)

@@ -17,7 +17,7 @@ int main(int argc, char** argv) {
 #define K(name) if (k == #name) { gp.name = (decltype(gp.name))v; continue; }
     K(seed) K(mb_w) K(mb_h) K(frames) K(slices_per_frame) K(idr_period) K(num_ref) K(transform_8x8) K(qp)
     K(cabac_init_idc) K(p_skip) K(p_intra_in_p) K(p_cbf) K(p_cbp) K(p_sig) K(p_last) K(p_gt1) K(p_gt1_more)
-    K(p_mvd_nz) K(p_mvd_more) K(p_dqp) K(p_t8x8) K(p_i16) K(long_startcodes) K(repeat_frame_num)
+    K(p_mvd_nz) K(p_mvd_more) K(p_dqp) K(p_t8x8) K(p_i16) K(long_startcodes) K(repeat_frame_num) K(p_bslice) K(p_direct)
 #undef K
     fprintf(stderr, "unknown key %s\n", k.c_str()); return 1;
   }

@@ -342,8 +342,9 @@ AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uin
   { AvrParRegs r; avr_par_engine_init(r); avr_par_store(r); }
   for (int x = 0; x < ps.sp.mb_w; x++) row[x].uid = 0;
   AvrParsePolicy io;
-  avr::SliceParser<AvrParsePolicy> parser(io, ps.sp, row, 1);
-  const int rc = parser.run();
+  int rc;
+  if (ps.sp.slice_type == avr::SLICE_B) { avr::SliceParser<AvrParsePolicy, true> parser(io, ps.sp, row, 1); rc = parser.run(); }
+  else { avr::SliceParser<AvrParsePolicy, false> parser(io, ps.sp, row, 1); rc = parser.run(); }
   res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted;
   const int over = g_par.nb > g_par.bin_cap || g_par.nblk > g_par.blk_cap;
   res->status = over ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;

@@ -67,7 +67,9 @@ struct GenIO {
   static int clampp(int p) { return p < 4 ? 4 : p > 252 ? 252 : p; }
   int prob(int ctx) const {
     int j = ((ctx * 37) & 63) - 32;
-    if (ctx >= 11 && ctx <= 13) return gp.p_skip;
+    if ((ctx >= 11 && ctx <= 13) || (ctx >= 24 && ctx <= 26)) return gp.p_skip;
+    if (ctx >= 27 && ctx <= 29) return 256 - gp.p_direct;     // first mb_type bin of a B slice: 0 = B_Direct_16x16
+    if (ctx == 36) return 256 - gp.p_direct;                  // first sub_mb_type bin: 0 = B_Direct_8x8
     if (ctx == 14) return gp.p_intra_in_p;
     if (ctx >= 3 && ctx <= 5) return gp.p_i16;
     if (ctx == 17) return gp.p_i16;
@@ -226,10 +228,11 @@ std::vector<uint8_t> generate_clip(const GenParams& gp) {
     for (int s = 0; s < nslices; s++) {
       const int first = (int)((int64_t)mbs * s / nslices), endmb = (int)((int64_t)mbs * (s + 1) / nslices);
       const bool islice = idr || rng.chance(12);
+      const bool bslice = !islice && gp.p_bslice > 0 && rng.chance(gp.p_bslice);
       SliceParams sp;
-      sp.slice_type = islice ? SLICE_I : SLICE_P;
+      sp.slice_type = islice ? SLICE_I : bslice ? SLICE_B : SLICE_P;
       sp.first_mb = first; sp.mb_w = gp.mb_w; sp.mb_h = gp.mb_h;
-      sp.num_ref[0] = islice ? 1 : avail_refs; sp.num_ref[1] = 1;
+      sp.num_ref[0] = islice ? 1 : avail_refs; sp.num_ref[1] = bslice ? avail_refs : 1;
       sp.cabac_init_idc = gp.cabac_init_idc;
       int qp_delta = rng.below(7) - 3;
       sp.slice_qp = gp.qp + qp_delta;
@@ -239,13 +242,16 @@ std::vector<uint8_t> generate_clip(const GenParams& gp) {
 
       BitWriter w;
       w.ue(first);
-      w.ue((islice ? 2 : 0) + (rng.chance(128) ? 5 : 0));
+      w.ue((islice ? 2 : bslice ? 1 : 0) + (rng.chance(128) ? 5 : 0));
       w.ue(0);
       w.u(log2_max_frame_num, frame_num);
       if (idr) w.ue(f & 0xFFFF);  // idr_pic_id
+      if (bslice) w.u(1, 1);                 // direct_spatial_mv_pred_flag
       if (!islice) {
         w.u(1, 1); w.ue(sp.num_ref[0] - 1);  // num_ref_idx_active_override
+        if (bslice) w.ue(sp.num_ref[1] - 1);
         w.u(1, 0);                           // ref_pic_list_modification_flag_l0
+        if (bslice) w.u(1, 0);               // ref_pic_list_modification_flag_l1
       }
       if (is_ref) {
         if (idr) { w.u(1, 0); w.u(1, 0); } else w.u(1, 0);

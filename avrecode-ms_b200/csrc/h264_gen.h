@@ -4,7 +4,7 @@
 // ships no test inputs (its README names data/GOPR4542.MP4, which is not in the repository).
 // This generator walks the same slice_data() state machine the product uses (h264_syntax.h)
 // with a seeded random bin source and a textbook CABAC encoder (cabac_std.h), so every clip
-// is a syntactically legal High-profile stream: SPS/PPS, IDR + P pictures (every picture a
+// is a syntactically legal High-profile stream: SPS/PPS, IDR + P (+ B, p_bslice) pictures (every picture a
 // reference, so frame_num changes on every picture), N slices per picture, optional 8x8
 // transform.  Legality is judged by the reference's own libavcodec accepting it
 // (tests/test_reference_parity.py runs oracle/_ref/recode on generated clips).
@@ -39,6 +39,8 @@ struct GenParams {
   int p_t8x8 = 128;
   int p_i16 = 96;              // P(intra macroblock is I16x16 rather than I_NxN)
   int long_startcodes = 1;     // 1: 4-byte start code on the first NAL of each picture
+  int p_bslice = 0;            // P(a non-IDR slice is a B slice); B pictures are reference pictures too, so frame_num keeps changing
+  int p_direct = 70;           // P(B_Direct_16x16) and P(B_Direct_8x8)
   int repeat_frame_num = 0;    // 1: non-reference pictures so consecutive pictures share frame_num (out-of-domain)
 };
 

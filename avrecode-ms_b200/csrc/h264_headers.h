@@ -67,7 +67,7 @@ struct SliceHeaderInfo {
   int nal_unit_type = 0, nal_ref_idc = 0;
   int pps_id = 0;
   bool cabac = false;
-  bool supported = true;     // false: B / field / MBAFF / FMO / high bit depth / 4:2:2+
+  bool supported = true;     // false: SP/SI / field / MBAFF / FMO / high bit depth / 4:2:2+
   size_t header_bits = 0;    // bits consumed by slice_header() in the RBSP (after the NAL header byte)
 };
 
@@ -291,7 +291,7 @@ static inline bool parse_slice_header(const uint8_t* rbsp, size_t nbits, int nal
   h.sp.transform_8x8_mode = pps.transform_8x8_mode;
   h.sp.chroma_format_idc = sps.chroma_format_idc;
   h.sp.direct_8x8_inference = sps.direct_8x8_inference;
-  h.supported = (st == 0 || st == 2) && !field_pic && !sps.mb_aff && sps.frame_mbs_only &&
+  h.supported = (st == 0 || st == 1 || st == 2) && !field_pic && !sps.mb_aff && sps.frame_mbs_only &&
                 pps.num_slice_groups == 1 && sps.chroma_format_idc <= 1 && sps.bit_depth_luma == 8 &&
                 sps.bit_depth_chroma == 8 && h.sp.mb_w <= AVR_MAX_MB_DIM && h.sp.mb_h <= AVR_MAX_MB_DIM &&
                 (int64_t)first_mb < (int64_t)h.sp.mb_w * (int64_t)h.sp.mb_h;

@@ -20,8 +20,11 @@
 // Policies: host CABAC decode + record (compress front end), device range decode + CABAC
 // re-encode (decompress kernel), random source + CABAC encode (clip generator).
 //
-// Supported: I and P slices, frame pictures (no MBAFF/field), chroma_format_idc 0/1,
-// transform_8x8_mode 0/1, multiple slices per picture, no I_PCM.  B slices: TODO (row 8f-4).
+// Supported: I, P and B slices (round 2: B_Skip / B_Direct_16x16 / the 21 two-list partition types / B_8x8 with its 13 sub
+// types; h264_cabac.c:1332-1370 skip contexts, :1973-2003 mb_type, :1455-1469 sub_mb_type, :1472-1501 ref_idx with the
+// direct_cache mask, :2112-2330 ref/mvd order), frame pictures (no MBAFF/field), chroma_format_idc 0/1,
+// transform_8x8_mode 0/1, multiple slices per picture, no I_PCM.  Direct prediction itself (motion vectors of direct blocks)
+// is never needed: direct blocks carry no mvd / ref_idx bins and are masked out of their neighbours' contexts.
 #pragma once
 #include "avr_common.h"
 
@@ -55,12 +58,15 @@ struct MbInfo {
   uint16_t cbp;          // bits0-3 luma 8x8, 4-5 chroma, 6/7 Cb/Cr DC coded, 8 luma DC coded
   uint8_t nnz[24];       // 16 luma (y*4+x), 4 Cb (y*2+x), 4 Cr : total_coeff per 4x4
   uint8_t refpos;        // bit (list*4 + b8): ref_idx > 0
-  uint8_t pad[3];
+  uint8_t direct8;       // bit b8: that 8x8 is direct-predicted (B_Skip / B_Direct_16x16: all four; B_8x8: its direct sub-blocks)
+  uint8_t pad[2];
   uint8_t mvd[2][16][2]; // [list][y*4+x][comp] = min(|mvd|, 70)
 };
 enum { MBF_SKIP = 1, MBF_INTRA = 2, MBF_I16 = 4, MBF_8x8DCT = 8, MBF_DIRECT = 16, MBF_PCM = 32 };
 
-template <class IO>
+// HAS_B = false compiles the B-slice branches out: the device kernels instantiate both and pick per slice, so that I / P
+// slices run the smaller code (the B branches cost the chain kernel 7 % on a P-only corpus: profiles/r02_summary.md).
+template <class IO, bool HAS_B = true>
 struct SliceParser {
   IO& io;
   const SliceParams& sp;
@@ -77,7 +83,7 @@ struct SliceParser {
 
   // ---- slice loop (h264_slice.c:2370-2440) ------------------------------------------------
   AVR_HDN int run() {
-    if (sp.slice_type != SLICE_P && sp.slice_type != SLICE_I) return SYN_E_SLICE_TYPE;
+    if (sp.slice_type != SLICE_P && sp.slice_type != SLICE_I && !(HAS_B && sp.slice_type == SLICE_B)) return SYN_E_SLICE_TYPE;
     int x = sp.first_mb % sp.mb_w, y = sp.first_mb / sp.mb_w;
     last_dqp_nz = 0;
     for (;;) {
@@ -115,6 +121,12 @@ struct SliceParser {
     if (by < 0) return T ? (T->refpos >> (list * 4 + 2 + (bx >> 1))) & 1 : 0;
     return (cur.refpos >> (list * 4 + (by >> 1) * 2 + (bx >> 1))) & 1;
   }
+  // sl->direct_cache of ffmpeg (h264_mvpred.h:723-753, h264_cabac.c:2131): is the 8x8 that holds 4x4 (bx,by) direct?
+  AVR_HD int direct_at(int bx, int by) const {
+    if (bx < 0) return L ? (L->direct8 >> ((by >> 1) * 2 + 1)) & 1 : 0;
+    if (by < 0) return T ? (T->direct8 >> (2 + (bx >> 1))) & 1 : 0;
+    return (cur.direct8 >> ((by >> 1) * 2 + (bx >> 1))) & 1;
+  }
   // luma4x4BlkIdx -> (x,y) in the 4x4 grid (6.4.3)
   static AVR_HD int blk_x(int i) { return (i & 1) | ((i >> 1) & 2); }
   static AVR_HD int blk_y(int i) { return ((i >> 1) & 1) | ((i >> 2) & 2); }
@@ -145,10 +157,23 @@ struct SliceParser {
     io.get(69); io.get(69); io.get(69);
   }
 
-  AVR_HDN int ref_idx(int list, int bx, int by) {  // h264_cabac.c:1472-1501 (P slices)
+  AVR_HDN int b_sub_mb_type() {  // h264_cabac.c:1455-1469
+    if (!io.get(36)) return 0;                       // B_Direct_8x8
+    if (!io.get(37)) return 1 + io.get(39);          // B_L0_8x8, B_L1_8x8
+    int type = 3;
+    if (io.get(38)) {
+      if (io.get(39)) return 11 + io.get(39);        // B_L1_4x4, B_Bi_4x4
+      type += 4;
+    }
+    type += 2 * io.get(39);
+    type += io.get(39);
+    return type;
+  }
+
+  AVR_HDN int ref_idx(int list, int bx, int by) {  // h264_cabac.c:1472-1501; direct neighbours do not count (B slices)
     int ctx = 0;
-    if (refpos_at(list, bx - 1, by)) ctx++;
-    if (refpos_at(list, bx, by - 1)) ctx += 2;
+    if (refpos_at(list, bx - 1, by) && !(HAS_B && direct_at(bx - 1, by))) ctx++;
+    if (refpos_at(list, bx, by - 1) && !(HAS_B && direct_at(bx, by - 1))) ctx += 2;
     int ref = 0;
     io.hint(HINT_REF_IDX, sp.num_ref[list] - 1);
     while (io.get(54 + ctx)) {
@@ -337,7 +362,7 @@ struct SliceParser {
     L = (x > 0 && row[x - 1].uid == uid) ? &row[x - 1] : nullptr;
     T = (y > 0 && row[x].uid == uid) ? &row[x] : nullptr;
     // T aliases row[x], which is overwritten at the end of this function only.
-    cur.uid = uid; cur.flags = 0; cur.chroma_pred = 0; cur.cbp = 0; cur.refpos = 0;
+    cur.uid = uid; cur.flags = 0; cur.chroma_pred = 0; cur.cbp = 0; cur.refpos = 0; cur.direct8 = 0;
     for (int i = 0; i < 24; i++) cur.nnz[i] = 0;
     for (int l = 0; l < 2; l++)
       for (int i = 0; i < 16; i++) cur.mvd[l][i][0] = cur.mvd[l][i][1] = 0;
@@ -345,17 +370,37 @@ struct SliceParser {
     const int decode_chroma = sp.chroma_format_idc == 1;
     int mbt_intra = -1;   // >=0: intra mb_type 0..25
     int p_type = -1;      // P: 0 16x16, 1 16x8, 2 8x16, 3 8x8
+    int b_type = -1;      // B: 0 B_Direct_16x16, 1..21 partition types (Table 7-14), 22 B_8x8
+    const int is_b = HAS_B && sp.slice_type == SLICE_B;
     if (sp.slice_type != SLICE_I) {
       int ctx = 0;
       if (L && !(L->flags & MBF_SKIP)) ctx++;
       if (T && !(T->flags & MBF_SKIP)) ctx++;
-      if (io.get(11 + ctx)) {  // mb_skip_flag
-        cur.flags = MBF_SKIP;
+      if (io.get((is_b ? 24 : 11) + ctx)) {  // mb_skip_flag (h264_cabac.c:1332-1370: +13 in B slices)
+        cur.flags = is_b ? (MBF_SKIP | MBF_DIRECT) : MBF_SKIP;   // B_Skip is direct-predicted
+        cur.direct8 = is_b ? 15 : 0;
         last_dqp_nz = 0;
         row[x] = cur;
         return 0;
       }
-      if (io.get(14) == 0) {
+      if (is_b) {                            // h264_cabac.c:1973-2003
+        int c = 0;
+        if (L && !(L->flags & MBF_DIRECT)) c++;
+        if (T && !(T->flags & MBF_DIRECT)) c++;
+        if (!io.get(27 + c)) b_type = 0;
+        else if (!io.get(27 + 3)) b_type = 1 + io.get(27 + 5);
+        else {
+          int bits = io.get(27 + 4) << 3;
+          bits |= io.get(27 + 5) << 2;
+          bits |= io.get(27 + 5) << 1;
+          bits |= io.get(27 + 5);
+          if (bits < 8) b_type = bits + 3;
+          else if (bits == 13) mbt_intra = intra_mb_type(32, 0);
+          else if (bits == 14) b_type = 11;
+          else if (bits == 15) b_type = 22;
+          else { bits = (bits << 1) | io.get(27 + 5); b_type = bits - 4; }
+        }
+      } else if (io.get(14) == 0) {
         if (io.get(15) == 0) p_type = 3 * io.get(16);
         else p_type = 2 - io.get(17);
       } else {
@@ -404,6 +449,74 @@ struct SliceParser {
         }
         cur.chroma_pred = (uint8_t)mode;
       }
+    } else if (HAS_B && b_type == 0) {  // B_Direct_16x16: no ref_idx, no mvd (h264_cabac.c:2218-2222)
+      cur.flags |= MBF_DIRECT;
+      cur.direct8 = 15;
+      dct8x8_allowed &= sp.direct_8x8_inference;
+    } else if (HAS_B && b_type == 22) {  // B_8x8 (h264_cabac.c:2112-2217)
+      int shape[4], lists[4];   // shape 0 8x8, 1 8x4, 2 4x8, 3 4x4 (as P sub types); lists bit0 L0, bit1 L1; 0 = direct
+      for (int i = 0; i < 4; i++) {
+        const int st = b_sub_mb_type();
+        // b_sub_mb_type_info (h264data.h:154-168), 2 bits per entry
+        shape[i] = (int)((0x3F99900u >> (2 * st)) & 3);
+        lists[i] = (int)((0x39FA5E4u >> (2 * st)) & 3);
+        if (st == 0) cur.direct8 |= (uint8_t)(1 << i);
+      }
+      for (int list = 0; list < 2; list++)
+        for (int i = 0; i < 4; i++) {
+          if (!(lists[i] & (1 << list))) continue;          // direct sub-blocks have lists == 0
+          int ref = 0;
+          if (sp.num_ref[list] > 1) {
+            ref = ref_idx(list, (i & 1) * 2, (i >> 1) * 2);
+            if (ref < 0) return ref;
+            if (ref >= sp.num_ref[list]) return SYN_E_REF;
+          }
+          set_ref(list, i, ref);
+        }
+      for (int i = 0; i < 4; i++)                            // get_dct8x8_allowed (h264.h)
+        if (lists[i] == 0 ? !sp.direct_8x8_inference : shape[i] != 0) dct8x8_allowed = 0;
+      for (int list = 0; list < 2; list++)
+        for (int i = 0; i < 4; i++) {
+          if (!(lists[i] & (1 << list))) continue;
+          int bx = (i & 1) * 2, by = (i >> 1) * 2, r = 0;
+          switch (shape[i]) {
+            case 0: r = mvd_partition(list, bx, by, 2, 2); break;
+            case 1: r = mvd_partition(list, bx, by, 2, 1); if (r >= 0) r = mvd_partition(list, bx, by + 1, 2, 1); break;
+            case 2: r = mvd_partition(list, bx, by, 1, 2); if (r >= 0) r = mvd_partition(list, bx + 1, by, 1, 2); break;
+            default:
+              for (int j = 0; j < 4 && r >= 0; j++) r = mvd_partition(list, bx + (j & 1), by + (j >> 1), 1, 1);
+          }
+          if (r < 0) return r;
+        }
+    } else if (HAS_B && b_type > 0) {  // B 16x16 / 16x8 / 8x16 with one or two lists per partition (h264_cabac.c:2223-2330)
+      // b_mb_type_info (h264data.h:128-152): types 1..3 = 16x16 L0 / L1 / Bi; 4..21 alternate 16x8 / 8x16 over nine list pairs
+      const int shp = b_type < 4 ? 0 : ((b_type & 1) ? 2 : 1);       // 0 16x16, 1 16x8, 2 8x16
+      const int pair = b_type < 4 ? 0 : (b_type - 4) >> 1;
+      const int use0 = b_type < 4 ? b_type : (int)((0x3F999u >> (2 * pair)) & 3);     // lists of partition 0: 1 L0, 2 L1, 3 both
+      const int use1 = b_type < 4 ? 0 : (int)((0x39F69u >> (2 * pair)) & 3);          // lists of partition 1
+      const int nparts = shp == 0 ? 1 : 2;
+      for (int list = 0; list < 2; list++)
+        for (int i = 0; i < nparts; i++) {
+          if (!((i ? use1 : use0) & (1 << list))) continue;
+          int bx = shp == 2 ? 2 * i : 0, by = shp == 1 ? 2 * i : 0;
+          int ref = 0;
+          if (sp.num_ref[list] > 1) {
+            ref = ref_idx(list, bx, by);
+            if (ref < 0) return ref;
+            if (ref >= sp.num_ref[list]) return SYN_E_REF;
+          }
+          if (shp == 0) { for (int b = 0; b < 4; b++) set_ref(list, b, ref); }
+          else if (shp == 1) { set_ref(list, 2 * i, ref); set_ref(list, 2 * i + 1, ref); }
+          else { set_ref(list, i, ref); set_ref(list, i + 2, ref); }
+        }
+      for (int list = 0; list < 2; list++)
+        for (int i = 0; i < nparts; i++) {
+          if (!((i ? use1 : use0) & (1 << list))) continue;
+          int bx = shp == 2 ? 2 * i : 0, by = shp == 1 ? 2 * i : 0;
+          int w = shp == 2 ? 2 : 4, h = shp == 1 ? 2 : 4;
+          int r = mvd_partition(list, bx, by, w, h);
+          if (r < 0) return r;
+        }
     } else if (p_type == 3) {  // P_8x8
       int sub[4];
       for (int i = 0; i < 4; i++) {  // h264_cabac.c:1432-1441

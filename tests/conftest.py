@@ -12,7 +12,7 @@ sys.path.insert(0, PKG)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 REF = os.path.join(ROOT, "oracle", "_ref")
-GOLDEN_NAMES = ["ip_basic", "multislice_multiref", "dct8x8", "dense_full_blocks", "skippy_idr"]
+GOLDEN_NAMES = ["ip_basic", "multislice_multiref", "dct8x8", "dense_full_blocks", "skippy_idr", "b_slices", "b_direct_multiref"]
 
 
 def pytest_configure(config):

@@ -17,6 +17,9 @@ CLIPS = {
     "dct8x8": "seed=103 mb_w=6 mb_h=4 frames=3 transform_8x8=1",
     "dense_full_blocks": "seed=104 mb_w=5 mb_h=3 frames=2 p_sig=250 p_last=2 p_cbf=250 p_cbp=250 transform_8x8=1",
     "skippy_idr": "seed=105 mb_w=10 mb_h=6 frames=5 p_skip=200 idr_period=2 qp=40 cabac_init_idc=2 slices_per_frame=2",
+    # round 2: B slices (every picture a reference, so frame_num keeps changing: inside the reference's own domain)
+    "b_slices": "seed=106 mb_w=8 mb_h=5 frames=5 p_bslice=190 num_ref=3 slices_per_frame=2 cabac_init_idc=1",
+    "b_direct_multiref": "seed=107 mb_w=7 mb_h=6 frames=6 p_bslice=220 p_direct=140 p_skip=90 num_ref=4",
 }
 for name, params in CLIPS.items():
     clip = os.path.join(HERE, name + ".h264")

@@ -136,7 +136,7 @@ def test_decompress_reference_containers(ctx):
 def test_batch_pipeline_equals_chain_and_oracle(ctx, tmpdir_path):
     import avr_ctypes as A
     params = [dict(seed=40 + i, mb_w=8 + 3 * i, mb_h=6 + i, frames=3 + i, slices_per_frame=1 + i % 3,
-                   transform_8x8=i % 2, num_ref=1 + i % 3) for i in range(6)]
+                   transform_8x8=i % 2, num_ref=1 + i % 3, p_bslice=(0, 0, 180, 220)[i % 4]) for i in range(6)]
     datas, wants = [], []
     for i, p in enumerate(params):
         clip = os.path.join(tmpdir_path, f"c{i}.h264")
@@ -230,6 +230,7 @@ IN_DOMAIN_SHAPES = [
     dict(seed=61, mb_w=240, mb_h=135, frames=2, slices_per_frame=68, p_sig=150, p_cbf=230, p_cbp=240),   # config 5 geometry, no 8x8
     dict(seed=62, mb_w=120, mb_h=68, frames=6, slices_per_frame=8, num_ref=3),                          # config 3 geometry
     dict(seed=2, mb_w=120, mb_h=68, frames=5, slices_per_frame=1),                                       # config 2 geometry
+    dict(seed=63, mb_w=120, mb_h=68, frames=4, slices_per_frame=8, num_ref=3, p_bslice=200),             # config 3 geometry with B slices
 ]
 
 
@@ -266,7 +267,7 @@ def test_reference_decompressor_accepts_our_container(ctx, tmpdir_path, name):
     """the survey's third oracle: a repo-written container fed to the reference DEcompressor (in-domain clips only: the
     reference cannot invert 8x8 blocks)"""
     import avr_ctypes as A
-    if name in ("dct8x8", "dense_full_blocks"):    # both generated with transform_8x8=1 (tests/golden/make_golden.py)
+    if name in ("dct8x8", "dense_full_blocks"):  # (the B-slice goldens are in the reference's domain: both run)    # both generated with transform_8x8=1 (tests/golden/make_golden.py)
         pytest.skip("reference decompressor does not invert 8x8-transform streams (recode.cpp:1215-1219 vs 1485-1487)")
     data = open(os.path.join(GOLDEN, name + ".h264"), "rb").read()
     comp, _ = A.compress_files(ctx, [data])

@@ -51,6 +51,8 @@ def test_pipeline_batch_of_files_keeps_models_separate():
     dict(seed=32, mb_w=16, mb_h=9, frames=12, transform_8x8=1, num_ref=4),          # > 95 symbols on many keys
     dict(seed=33, mb_w=11, mb_h=7, frames=6, idr_period=2, qp=12, cabac_init_idc=1),
     dict(seed=34, mb_w=7, mb_h=5, frames=3, p_sig=252, p_last=1, p_cbf=254, p_cbp=254, transform_8x8=1),  # full blocks
+    dict(seed=35, mb_w=13, mb_h=8, frames=7, p_bslice=200, num_ref=4, slices_per_frame=3, transform_8x8=1),  # B slices, two lists, 8x8
+    dict(seed=36, mb_w=9, mb_h=9, frames=6, p_bslice=230, p_direct=160, p_skip=120, num_ref=2, cabac_init_idc=2),  # direct-heavy B
 ])
 def test_bodies_match_oracle_on_fresh_clips(params, tmpdir_path):
     clip = os.path.join(tmpdir_path, "c.h264")
