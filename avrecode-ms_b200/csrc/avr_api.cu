@@ -271,7 +271,7 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
   uint64_t nbins = 0, nblocks = 0, nframes = 0, emitted = 0, chain_mbs = 0, pic_mbs = 0, scratch = 0;
   for (int f = 0; f < nfiles; f++) {
     const avr::FileRecord& r = recs[f]->rec;
-    if (r.error || r.out_of_domain) { avr_set_error("file %d: record not compressible (error %d, out_of_domain %d)", f, r.error, r.out_of_domain); delete b; return AVR_E_UNSUPPORTED; }
+    if (r.error || (r.out_of_domain & 1)) { avr_set_error("file %d: record not compressible (error %d, out_of_domain %d)", f, r.error, r.out_of_domain); delete b; return AVR_E_UNSUPPORTED; }
     AvrFileDesc& fd = fds[f];
     memset(&fd, 0, sizeof fd);
     fd.bin_off = nbins; fd.nbins = (uint32_t)r.bins.size();
@@ -670,7 +670,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   par_for(nfiles, host_threads, [&](int f) {
     AvrFileScan& sc = bf->scans[f];
     sc.rc = avr::scan_annexb(files[f], lens[f], &sc.rec, &sc.coded);
-    if (!sc.rc && sc.rec.out_of_domain) sc.rc = AVR_E_UNSUPPORTED;
+    if (!sc.rc && (sc.rec.out_of_domain & 1)) sc.rc = AVR_E_UNSUPPORTED;
   });
   avr_trace("cf: host scan");
   // layout of the pools.  AVR_TEST_PARSE_CAP (tests only) lowers the record capacity so that the overflow -> host

@@ -319,7 +319,7 @@ static int compress_core(const std::vector<avr_context*>& lanes, const uint8_t* 
     const int i = rest[k];
     recs[i] = avr_record_new();
     rec_rc[i] = avr_record_annexb(recs[i], in[i], in_len[i]);
-    if (avr_record_view(recs[i])->out_of_domain) rec_rc[i] = AVR_E_UNSUPPORTED;
+    if (avr_record_view(recs[i])->out_of_domain & 1) rec_rc[i] = AVR_E_UNSUPPORTED;
   });
   tt.host_ms += now_ms() - t_host0;
   auto cleanup = [&]() { for (auto r : recs) if (r) avr_record_free(r); };
@@ -439,7 +439,7 @@ static int decompress_core(const std::vector<avr_context*>& lanes, const uint8_t
     int nflips = 0; bool last_prev_valid = false;
     int rc = avr::scan_annexb_slices(d.surrogate.data(), d.surrogate.size(), [&](const avr::SliceLoc& loc) -> int {
       const avr::SliceHeaderInfo& sh = loc.sh;
-      if (sh.sp.first_mb == 0 && !(have && sh.sp.mb_w == w && sh.sp.mb_h == h && sh.frame_num == fnum)) {   // update_frame_spec
+      if (sh.sp.first_mb == 0 && !(avr::strict_domain() && have && sh.sp.mb_w == w && sh.sp.mb_h == h && sh.frame_num == fnum)) {   // update_frame_spec; every picture flips unless AVR_STRICT_DOMAIN (avr_record.h)
         last_prev_valid = have && sh.sp.mb_w == w && sh.sp.mb_h == h;
         nflips++;
         have = true; w = sh.sp.mb_w; h = sh.sp.mb_h; fnum = sh.frame_num;

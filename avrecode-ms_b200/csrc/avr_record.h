@@ -4,6 +4,7 @@
 // driven either by libavcodec-hooks itself or by the native parser
 // (avr_record.cpp).
 #pragma once
+#include <stdlib.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <vector>
@@ -29,9 +30,15 @@ struct FileRecord {
   std::vector<SliceSpan> spans;
   uint64_t source_bins = 0;   // get/get_bypass/get_terminate calls on coded slices (SURVEY 8d "bin")
   uint64_t emitted = 0;       // symbols that go through the range coder: bins minus EOB bins plus nnz side-channel bits
-  int out_of_domain = 0;      // bit0: consecutive pictures share frame_num (recode.cpp:831-834 skips bzero)
+  int out_of_domain = 0;      // bit0: consecutive pictures share frame_num and AVR_STRICT_DOMAIN=1: not compressible (literal)
+                              // bit1: they do, and the picture was given its own store (extended domain, see frame_spec)
   int error = 0;              // AVR_E_* from the parse
 };
+
+inline bool strict_domain() {
+  static const bool on = [] { const char* e = getenv("AVR_STRICT_DOMAIN"); return e && e[0] == '1'; }();
+  return on;
+}
 
 class Recorder {
  public:
@@ -40,8 +47,14 @@ class Recorder {
   // ModelHooks::frame_spec -> h264_model::update_frame_spec (recode.cpp:831-850)
   void frame_spec(int frame_num, int mb_w, int mb_h) {
     if (have_ && mb_w == w_ && mb_h == h_ && frame_num == frame_num_) {
-      r_->out_of_domain |= 1;
-      return;
+      // The reference does NOT flip here (recode.cpp:832-834), keeps the previous picture's significance flags and
+      // counts them (:942-954): its compressor's output for such streams (non-reference B pictures, all-IDR streams)
+      // cannot be decompressed by anyone, its own decompressor included (as shipped it aborts on the assert at
+      // :1040).  There is no reference result to be identical to, so by default every picture gets its own zeroed store
+      // like any other -- both directions of this library agree on that rule and the stream round-trips.
+      // AVR_STRICT_DOMAIN=1 keeps to the reference's domain instead: the file is stored as a literal block.
+      if (strict_domain()) { r_->out_of_domain |= 1; return; }
+      r_->out_of_domain |= 2;
     }
     AvrFrame f;
     f.mb_w = (uint16_t)mb_w; f.mb_h = (uint16_t)mb_h;

@@ -334,3 +334,32 @@ def test_lanes_and_multi_context_give_the_same_containers(ctx, tmpdir_path, monk
     exe = os.path.join(ROOT, "avrecode-ms_b200", "bin", "recode")
     paths = [os.path.join(tmpdir_path, f"m{i}.h264") for i in range(0, 160, 2) if i != 7]
     assert run([exe, "roundtrip-batch", "--gpus", "2"] + paths)[0] == 0
+
+
+@pytest.mark.parametrize("params", [
+    dict(seed=81, mb_w=12, mb_h=9, frames=9, repeat_frame_num=1, slices_per_frame=2),                       # non-reference P pictures
+    dict(seed=82, mb_w=10, mb_h=8, frames=8, repeat_frame_num=1, p_bslice=180, num_ref=2, transform_8x8=1),   # non-reference B pictures
+])
+def test_repeated_frame_num_round_trips_where_the_reference_cannot(ctx, tmpdir_path, params):
+    """consecutive pictures sharing frame_num (non-reference pictures): the reference skips the store reset (recode.cpp:832-834),
+    counts stale flags and cannot decompress its own output.  Here every picture gets its own store in both
+    directions: the stream is coded (not stored literally) and round-trips.  AVR_STRICT_DOMAIN=1 is covered by
+    tests/test_host_logic.py (a fresh process: the switch is read once)."""
+    import avr_ctypes as A
+    clip = os.path.join(tmpdir_path, "rf.h264")
+    data = gen_clip(clip, **params)
+    if have_ref():
+        assert run([os.path.join(REF, "recode"), "roundtrip", clip])[0] != 0, "the reference round-trips this clip after all?"
+    comp, tc = A.compress_files(ctx, [data])
+    assert any("cabac" in b for b in parse_avrec(comp[0])) and len(comp[0]) < len(data)
+    back, _ = A.decompress_files(ctx, comp)
+    assert back[0] == data
+    rec = A.Record(data)
+    assert rec.rc == 0 and rec.out_of_domain == 2
+    rec.close()
+    # the reference's domain only: a literal block, still a valid container
+    exe = os.path.join(ROOT, "avrecode-ms_b200", "bin", "recode")
+    lit, rt = os.path.join(tmpdir_path, "lit.avrec"), os.path.join(tmpdir_path, "rt.h264")
+    assert run([exe, "compress", clip, lit], env=dict(os.environ, AVR_STRICT_DOMAIN="1"))[0] == 0
+    assert all("cabac" not in b for b in parse_avrec(open(lit, "rb").read()))
+    assert run([exe, "decompress", lit, rt])[0] == 0 and open(rt, "rb").read() == data

@@ -94,3 +94,18 @@ def test_header_fuzz_and_advisor_repro_stay_inside_buffers(tmpdir_path):
         for seed in range(1, 9):
             rc, out, err = run([EMUL_ASAN, "scanraw", os.path.join(GOLDEN, name + ".h264"), str(seed), "24"], timeout=120)
             assert rc == 0 and b"TERMINATED" in out and b"ERROR" not in err and b"runtime error" not in err, out + err
+
+
+def test_repeated_frame_num_extended_and_strict_domain(tmpdir_path):
+    """avr_record.h frame_spec: by default a picture that repeats frame_num gets its own store (flag 2, the bodies round-trip);
+    AVR_STRICT_DOMAIN=1 keeps to the reference's domain (flag 1: the file API stores such a file as a literal block)"""
+    clip = os.path.join(tmpdir_path, "rf.h264")
+    gen_clip(clip, seed=83, mb_w=9, mb_h=7, frames=8, repeat_frame_num=1, p_bslice=150, num_ref=2)
+    tool = os.path.join(ROOT, "avrecode-ms_b200", "bin", "avrtool")
+    rc, _, err = run([tool, "stats", clip])
+    assert rc == 0 and b"ood=2" in err, err
+    rc, _, err = run([tool, "stats", clip], env=dict(os.environ, AVR_STRICT_DOMAIN="1"))
+    assert b"ood=1" in err, err
+    for cmd in ("roundtrip", "parse"):
+        rc, out, err = run([EMUL, cmd, clip])
+        assert rc == 0 and out.startswith(b"OK"), out + err
