@@ -234,6 +234,21 @@ struct DevMem {
 static float ev_ms(cudaEvent_t a, cudaEvent_t b) { float ms = 0; cudaEventElapsedTime(&ms, a, b); return ms; }
 
 // ---- compress batch ---------------------------------------------------------------------------
+// Pass D is serial per slice.  A slice of up to this many bins shares a warp with 31 others of similar length (one slice per
+// lane, in lockstep: ~15x fewer issue slots per symbol); a longer one keeps a warp to itself, because a lockstep step costs
+// ~4x the latency of a lone lane's step and the kernel lasts as long as its slowest warp (profiles/r02_summary.md).
+// Threshold: a packed warp should not outlast the longest lone slice of the batch.  Measured on the 1024-clip bench corpus
+// (longest slice 0.9 Mbins; pass D ms at thresholds 0 / 150k / 400k / 500k / 800k / all packed: 87 / 76 / 68 / 85 / 134 / 167), i.e. the
+// optimum sits at ~0.45 x the longest slice; AVR_CODE_LANE_MAX overrides it.
+static uint32_t code_long_of(const std::vector<AvrBatchSlice>& bsl, const std::vector<uint32_t>& order) {
+  if (order.empty()) return 0;
+  static const long env = [] { const char* e = getenv("AVR_CODE_LANE_MAX"); return e && *e ? atol(e) : -1L; }();
+  const uint32_t longest = bsl[order[0]].bin_end - bsl[order[0]].bin_start;
+  const uint32_t lane_max = env >= 0 ? (uint32_t)env : (uint32_t)(0.45 * longest);
+  uint32_t n = 0;
+  while (n < order.size() && bsl[order[n]].bin_end - bsl[order[n]].bin_start > lane_max) n++;
+  return n;
+}
 static std::vector<uint32_t> code_order_of(const std::vector<AvrBatchSlice>& bsl) {
   std::vector<uint32_t> o(bsl.size());
   for (uint32_t i = 0; i < o.size(); i++) o[i] = i;
@@ -323,6 +338,7 @@ extern "C" int avr_cbatch_create(avr_context* ctx, const avr_record* const* recs
   uint32_t* d_order; if ((rc = m.alloc(&d_order, bsl.size()))) return fail(rc);
   d.code_order = d_order;
   const std::vector<uint32_t> order = code_order_of(bsl);
+  d.code_long = code_long_of(bsl, order);
   d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
   // upload (timed: this is the H2D leg of the e2e number)
   cudaStream_t st = ctx->stream;
@@ -790,6 +806,7 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   uint32_t* d_corder; if ((rc = m.alloc(&d_corder, bsl.size()))) return fail(rc);
   d.code_order = d_corder;
   const std::vector<uint32_t> corder = code_order_of(bsl);
+  d.code_long = code_long_of(bsl, corder);
   d.scratch_off = b->d_scratch_off; d.scratch_cap = b->d_scratch_cap;
   cudaEventRecord(ctx->ev[0], st);
   auto up = [&](void* dst, const void* src, size_t n) { if (n) cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, st); h2d += n; };

@@ -256,11 +256,12 @@ __global__ void __launch_bounds__(256) avr_k_estimate(const uint32_t* sorted, co
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) avr_body_estimate(i, sorted, idx, head, P, fn, prob);
 }
-// One slice per warp, coded by lane 0: the one inherently serial pass.  (One slice per LANE made every step of the
-// warp pay for the renormalisation of whichever lane needed it -- about one symbol in nine per lane, so nearly every
-// step of 32 -- and for the longest slice of the 32.)  The exact-division table is staged in shared memory by the warp.
-// Launch order: longest slice first.
-__global__ void __launch_bounds__(32) avr_k_code(AvrPipe a, const uint32_t* order) {
+// Pass D, the one inherently serial pass.  Round 1 coded one slice per warp on lane 0 (one slice per LANE made every step of the
+// warp pay for the renormalisation of whichever lane needed it, and the kernel lasted as long as the warp that held the longest
+// slices).  Round 2 is a hybrid over the launch order (longest slice first): the first `nlong` slices keep a warp each, the others
+// are packed 32 to a warp, neighbours in the order and therefore of similar length.  The exact-division table is staged in shared
+// memory by the warp.
+__global__ void __launch_bounds__(32) avr_k_code(AvrPipe a, const uint32_t* order, uint32_t nlong) {
   __shared__ AvrDivTab dt;
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(&a.tab->hot.div);
@@ -268,8 +269,12 @@ __global__ void __launch_bounds__(32) avr_k_code(AvrPipe a, const uint32_t* orde
     for (uint32_t i = threadIdx.x; i < sizeof(AvrDivTab) / 4; i += 32) dst[i] = src[i];
   }
   __syncwarp();
-  if (blockIdx.x >= a.nslices || threadIdx.x != 0) return;
-  avr_body_code(a, order ? order[blockIdx.x] : blockIdx.x, &dt);
+  if (blockIdx.x < nlong) {
+    if (threadIdx.x == 0) avr_body_code(a, order ? order[blockIdx.x] : blockIdx.x, &dt);
+    return;
+  }
+  const uint32_t i = nlong + (blockIdx.x - nlong) * 32u + threadIdx.x;
+  if (i < a.nslices) avr_body_code(a, order ? order[i] : i, &dt);
 }
 
 size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bit) {
@@ -318,7 +323,10 @@ int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* lau
   AVR_CK(cub::DeviceScan::InclusiveScan(b.cub_tmp, tmp, fe, b.fn, AvrHalfSegOp(), (int)n, st)); nl += 2;
   avr_k_estimate<<<(n + 255) / 256, 256, 0, st>>>(b.keys_b, b.idx_b, b.head, b.psum, b.fn, b.prob, n); nl++;
   if (coder_begin) cudaEventRecord(coder_begin, st);
-  avr_k_code<<<b.nslices, 32, 0, st>>>(a, b.code_order); nl++;
+  {
+    const uint32_t nlong = b.code_order ? (b.code_long < b.nslices ? b.code_long : b.nslices) : b.nslices;
+    avr_k_code<<<nlong + (b.nslices - nlong + 31) / 32, 32, 0, st>>>(a, b.code_order, nlong); nl++;
+  }
   if (coder_end) cudaEventRecord(coder_end, st);
   if (launches) *launches = nl;
   return (int)cudaGetLastError();

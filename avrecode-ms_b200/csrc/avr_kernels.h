@@ -17,6 +17,7 @@ struct AvrDevBatch {
   const AvrSlice* slices;          // file-local slice table (chain kernel)
   const AvrBatchSlice* bslices;    // batch-global slice table (pipeline)
   const uint32_t* code_order;      // slices by descending bin count (pass D launch order), or null
+  uint32_t code_long;              // the first code_long slices of that order are coded one per WARP, the rest one per LANE
   const AvrFrame* frames;
   const AvrTables* tab;
   // chain kernel state
