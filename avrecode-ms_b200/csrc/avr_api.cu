@@ -491,6 +491,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   std::vector<AvrDecSlice> ds;
   uint64_t pay = 0, outb = 0, chain_mbs = 0;
   uint32_t s = 0;
+  int has_b = 0;
   for (int f = 0; f < nfiles; f++) {
     AvrFileDesc& fd = fds[f];
     memset(&fd, 0, sizeof fd);
@@ -506,6 +507,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
       d.payload_off = pay; d.payload_len = in.payload_len; pay += ((uint64_t)in.payload_len + 15) & ~15ull;
       d.out_off = outb; d.out_cap = in.size + 64; outb += ((uint64_t)d.out_cap + 15) & ~15ull;
       d.flip = in.flip; d.sp = to_sp(&in.sp);
+      if (d.sp.slice_type == avr::SLICE_B) has_b = 1;
       uint32_t mbs = (uint32_t)in.sp.mb_w * (uint32_t)in.sp.mb_h;
       if (mbs > fd.max_mbs) fd.max_mbs = mbs;
       ds.push_back(d);
@@ -518,7 +520,7 @@ extern "C" int avr_dbatch_create(avr_context* ctx, const avr_dslice* slices, con
   b->out_bytes = outb;
   AvrDevDBatch& d = b->d;
   DevMem& m = b->mem;
-  d.nfiles = nfiles; d.nslices = (uint32_t)ds.size(); d.tab = ctx->d_tab;
+  d.nfiles = nfiles; d.nslices = (uint32_t)ds.size(); d.tab = ctx->d_tab; d.has_b = has_b;
   avr_trace(nullptr);
   AvrFileDesc* d_fds; AvrDecSlice* d_ds; uint8_t* d_pay;
   int rc;
@@ -745,7 +747,9 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   cudaMemcpyAsync(d_row_off, row_off.data(), ns * sizeof(uint64_t), cudaMemcpyHostToDevice, st); h2d += ns * 8;
   cudaMemcpyAsync(d_order, order.data(), ns * sizeof(uint32_t), cudaMemcpyHostToDevice, st); h2d += ns * 4;
   cudaEventRecord(ctx->ev[1], st);
-  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, d_order, st);
+  int has_b = 0;
+  for (const AvrParseSlice& q : ps) if (q.sp.slice_type == avr::SLICE_B) has_b = 1;
+  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, d_order, has_b, st);
   cudaEventRecord(ctx->ev[2], st);
   if (rc) { avr_set_error("parse launch: %s", cudaGetErrorString((cudaError_t)rc)); return fail(AVR_E_CUDA); }
   std::vector<AvrParseResult> res(ns);

@@ -586,6 +586,9 @@ AVR_DEC_INL void avr_dec_flip_zero(const AvrDecSlice& ds, int lane, int nlanes) 
 // One coded slice on the chain thread.  g_dec.st must hold the slice's initial CABAC states and the
 // encoder thread must be consuming the ring.  Returns AVR_OK or an error (after an error the model
 // state of the file is meaningless).  The CABAC byte count / overflow flag come from the encoder.
+// HAS_B: a kernel that holds BOTH parser instances runs I/P slices 26 % slower (one chain) than one that holds only the I/P
+// instance (same-box A/B, profiles/r02_summary.md), so the instance is chosen per KERNEL and the host picks the kernel per batch.
+template <bool HAS_B>
 AVR_DEC_FN int avr_dec_slice(const AvrDecSlice& ds, const uint8_t* payloads, avr::MbInfo* row, uint32_t uid, uint32_t* out_bins) {
   if (uid == 1) for (int x = 0; x < ds.sp.mb_w; x++) row[x].uid = 0;
   avr_dec_init_range(payloads + ds.payload_off, ds.payload_len);
@@ -593,8 +596,7 @@ AVR_DEC_FN int avr_dec_slice(const AvrDecSlice& ds, const uint8_t* payloads, avr
   const uint32_t head0 = g_dec.ring_head;                      // every bin posts exactly one record
   AvrDecPolicy io;
   int rc;
-  if (ds.sp.slice_type == avr::SLICE_B) { avr::SliceParser<AvrDecPolicy, true> parser(io, ds.sp, row, uid); rc = parser.run(); }
-  else { avr::SliceParser<AvrDecPolicy, false> parser(io, ds.sp, row, uid); rc = parser.run(); }
+  { avr::SliceParser<AvrDecPolicy, HAS_B> parser(io, ds.sp, row, uid); rc = parser.run(); }
   *out_bins = g_dec.ring_head - head0;
   if (!g_dec.done) avr_ring_post(AVR_REC_ABORT, 0);            // release the encoder thread
 #if defined(AVR_ENC_BATCH)
@@ -622,7 +624,7 @@ static void avr_decompress_file_host(const AvrFileDesc& fd, const AvrDecSlice* s
     avr_cabac_init_states(g_dec.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, 0, 1);
     g_cab_host.low = 0; g_cab_host.range = (1u << 22) * 0x1FEu; g_cab_host.n = 0; g_cab_host.cap = ds.out_cap;
     g_cab_host.out = out + ds.out_off; g_cab_host.err = 0;
-    int rc = avr_dec_slice(ds, payloads, row, ++uid, &out_bins[g]);
+    int rc = avr_dec_slice<true>(ds, payloads, row, ++uid, &out_bins[g]);
     out_len[g] = g_cab_host.n;
     status[g] = rc ? rc : g_cab_host.err;
     if (status[g]) failed = 1;

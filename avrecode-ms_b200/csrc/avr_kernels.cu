@@ -39,6 +39,7 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
 #define AVR_CHAIN_TID 0
 #define AVR_ENC_TID 32
 #endif
+template <bool HAS_B>
 __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     const AvrFileDesc* fds, int nfiles, const AvrDecSlice* slices, const uint8_t* payloads, uint16_t* est_pool,
     uint8_t* store_pool, avr::MbInfo* row_pool, const AvrTables* tab, uint8_t* out, uint32_t* out_len, uint32_t* out_bins,
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     avr_cabac_init_states(g_dec.st, tab, ds.sp.slice_type == avr::SLICE_I, ds.sp.cabac_init_idc, ds.sp.slice_qp, tid, AVR_DEC_THREADS);
     __syncthreads();
     int rc = 0;
-    if (tid == AVR_CHAIN_TID) rc = avr_dec_slice(ds, payloads, row_pool + fd.mb_base, ++uid, &out_bins[g]);
+    if (tid == AVR_CHAIN_TID) rc = avr_dec_slice<HAS_B>(ds, payloads, row_pool + fd.mb_base, ++uid, &out_bins[g]);
     else if (tid == AVR_ENC_TID) avr_cab_encoder_thread(out + ds.out_off, ds.out_cap);
     __syncthreads();
     if (tid == AVR_CHAIN_TID) {
@@ -95,6 +96,7 @@ __global__ void __launch_bounds__(128) avr_k_patch_tails(const AvrParseSlice* ps
 }
 // Compress-side parse on the device (avr_parse.h): one warp per coded slice, lane 0 walks the slice,
 // all lanes initialise the CABAC states and tables.
+template <bool HAS_B>
 __global__ void __launch_bounds__(32) avr_k_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool,
                                                   AvrBlock* blk_pool, avr::MbInfo* row_pool, const uint64_t* row_off,
                                                   const AvrTables* tab, AvrParseResult* res, const uint32_t* order) {
@@ -105,7 +107,7 @@ __global__ void __launch_bounds__(32) avr_k_parse(const AvrParseSlice* ps, uint3
   avr_par_tables(tab, (int)lane, 32);
   avr_cabac_init_states(g_par.st, tab, p.sp.slice_type == avr::SLICE_I, p.sp.cabac_init_idc, p.sp.slice_qp, (int)lane, 32);
   __syncwarp();
-  if (lane == 0) avr_parse_slice(p, raw, bins_pool, blk_pool, row_pool + row_off[s], &res[s]);
+  if (lane == 0) avr_parse_slice<HAS_B>(p, raw, bins_pool, blk_pool, row_pool + row_off[s], &res[s]);
 }
 // capacity block pool -> dense block array
 __global__ void __launch_bounds__(128) avr_k_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count,
@@ -187,7 +189,7 @@ int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
     cudaFuncAttributes fa;
     int pct = -1;
     if (const char* e = getenv("AVR_DEC_CARVEOUT")) pct = atoi(e);
-    else if (cudaFuncGetAttributes(&fa, avr_k_decompress_chain) == cudaSuccess) {
+    else if (cudaFuncGetAttributes(&fa, b.has_b ? avr_k_decompress_chain<true> : avr_k_decompress_chain<false>) == cudaSuccess) {
       const int hint = g_chain_hint.load(), chains = hint > b.nfiles ? hint : b.nfiles;   // launches of other lanes share the SMs
       const int per_sm = (chains + sms - 1) / sms;
       const size_t need = (size_t)per_sm * (fa.sharedSizeBytes + 1024);      // + the per-block reservation
@@ -196,9 +198,12 @@ int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
       // chains bring: 2048-clip corpus, 606 ms at 70 % (all chains resident), 594 at 60 %, 588 at 50 % (profiles/r02_summary.md)
       if (pct > 50) pct = 50;
     }
-    if (pct >= 0) cudaFuncSetAttribute(avr_k_decompress_chain, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+    if (pct >= 0) cudaFuncSetAttribute(b.has_b ? avr_k_decompress_chain<true> : avr_k_decompress_chain<false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
   }
-  avr_k_decompress_chain<<<b.nfiles, AVR_DEC_THREADS, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
+  // the kernel with the B-slice parser instance only when the batch holds a B slice (avr_decode.h avr_dec_slice)
+  if (b.has_b) avr_k_decompress_chain<true><<<b.nfiles, AVR_DEC_THREADS, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
+                                                 b.tab, b.out, b.out_len, b.out_bins, b.status, b.file_order);
+  else avr_k_decompress_chain<false><<<b.nfiles, AVR_DEC_THREADS, 0, st>>>(b.fds, b.nfiles, b.slices, b.payloads, b.est_pool, b.store_pool, b.row_pool,
                                                  b.tab, b.out, b.out_len, b.out_bins, b.status, b.file_order);
   return (int)cudaGetLastError();
 }
@@ -334,7 +339,7 @@ int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* lau
 
 int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
                      avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, const uint32_t* order,
-                     cudaStream_t st) {
+                     int has_b, cudaStream_t st) {
   if (n == 0) return 0;
   avr_k_patch_tails<<<(n + 127) / 128, 128, 0, st>>>(ps, n, raw);
   // Registers allow 28 one-warp blocks per SM, but with that many walkers at different places of the syntax code the
@@ -345,7 +350,8 @@ int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const size_t dyn = n > (uint32_t)sms * 12u ? 16000 : 0;
-  avr_k_parse<<<n, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
+  if (has_b) avr_k_parse<true><<<n, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
+  else avr_k_parse<false><<<n, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
   return (int)cudaGetLastError();
 }
 int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,

@@ -333,6 +333,7 @@ struct AvrParsePolicy {
 
 // One slice on one thread.  g_par.st / tables must be initialised by the caller (cooperatively in
 // the kernel).  row = [mb_w] MbInfo scratch private to this slice (neighbours never cross slices).
+template <bool HAS_B>
 AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
                                 avr::MbInfo* row, AvrParseResult* res) {
   g_par.in = raw + ps.raw_off; g_par.size = ps.size;
@@ -343,8 +344,7 @@ AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uin
   for (int x = 0; x < ps.sp.mb_w; x++) row[x].uid = 0;
   AvrParsePolicy io;
   int rc;
-  if (ps.sp.slice_type == avr::SLICE_B) { avr::SliceParser<AvrParsePolicy, true> parser(io, ps.sp, row, 1); rc = parser.run(); }
-  else { avr::SliceParser<AvrParsePolicy, false> parser(io, ps.sp, row, 1); rc = parser.run(); }
+  { avr::SliceParser<AvrParsePolicy, HAS_B> parser(io, ps.sp, row, 1); rc = parser.run(); }
   res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted;
   const int over = g_par.nb > g_par.bin_cap || g_par.nblk > g_par.blk_cap;
   res->status = over ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;

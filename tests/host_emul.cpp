@@ -238,7 +238,7 @@ static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& 
     avr_cabac_init_states(g_par.st, &tab, c.sp.slice_type == avr::SLICE_I, c.sp.cabac_init_idc, c.sp.slice_qp, 0, 1);
     AvrParseResult res;
     avr_body_patch_tail(ps, raw.data());
-    avr_parse_slice(ps, raw.data(), b.data(), k.data(), row.data(), &res);
+    avr_parse_slice<true>(ps, raw.data(), b.data(), k.data(), row.data(), &res);
     if (fuzz_flips) { with_status += res.status != 0; continue; }
     if (res.status) { printf("slice status %d\n", res.status); return 1; }
     bins.insert(bins.end(), b.begin(), b.begin() + res.nbins);
