@@ -19,7 +19,7 @@ rows = [r for r in csv.reader(open("$R/gpurun_out/r02_counters.csv")) if len(r) 
 hdr = rows[0]; iK = hdr.index("Kernel Name"); iM = hdr.index("Metric Name"); iV = hdr.index("Metric Value"); iU = hdr.index("Metric Unit")
 agg = {}
 for r in rows[1:]:
-    k = r[iK].split("(")[0]; v = float(r[iV].replace(",", "")); u = r[iU]
+    k = r[iK].split("(")[0].replace("void ", "").split("<")[0].strip(); v = float(r[iV].replace(",", "")); u = r[iU]
     if r[iM].startswith("gpu__time_duration"): v = v / 1e6 if u in ("ns", "nsecond") else v / 1e3 if u in ("us", "usecond") else v
     if r[iM].startswith("dram__bytes"): v = v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
     agg.setdefault(k, {}).setdefault(r[iM], []).append(v)
