@@ -179,6 +179,7 @@ void avr_set_chain_concurrency_hint(int files) { g_chain_hint = files; }
 
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st) {
   if (b.nfiles == 0) return 0;
+  if (const char* e = getenv("AVR_DEC_SPEC")) if (e[0] == '1') return avr_launch_decompress_chain_spec(b, st);   // experimental kernel (avr_kernels_spec.cu)
   {
     // L1 and shared memory are one 256 KB array per SM.  Left alone the driver carves out shared memory for as many
     // blocks as registers allow (14 x 10 KB), which leaves the chains' estimator cells ~90 KB of L1; a batch that puts

@@ -57,6 +57,7 @@ int avr_launch_compress_chain(const AvrDevBatch& b, cudaStream_t st);
 int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* launches, cudaEvent_t coder_begin, cudaEvent_t coder_end);
 size_t avr_pipeline_tmp_bytes(uint32_t nemit, uint32_t nentries, int sort_end_bit);
 int avr_launch_decompress_chain(const AvrDevDBatch& b, cudaStream_t st);
+int avr_launch_decompress_chain_spec(const AvrDevDBatch& b, cudaStream_t st);   // avr_kernels_spec.cu (experimental, AVR_DEC_SPEC=1)
 int avr_launch_compact(const uint8_t* scratch, const uint64_t* scratch_off, const uint32_t* len, uint64_t* out_off,
                        uint64_t* total, uint8_t* out, uint32_t n, cudaStream_t st);
 int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,

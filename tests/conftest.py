@@ -22,7 +22,7 @@ def pytest_configure(config):
 @pytest.fixture(scope="session", autouse=True)
 def built():
     need = [os.path.join(PKG, "libavrecode_b200.so"), os.path.join(PKG, "bin", "avrgen"),
-            os.path.join(ROOT, "build", "avr_emul"), os.path.join(ROOT, "build", "avr_emul_asan"),
+            os.path.join(ROOT, "build", "avr_emul"), os.path.join(ROOT, "build", "avr_emul_asan"), os.path.join(ROOT, "build", "avr_emul_spec"),
             os.path.join(REF, "avr_oracle")]
     if not all(os.path.exists(p) for p in need):
         import __graft_entry__ as g

@@ -13,7 +13,11 @@
 #include "../avrecode-ms_b200/csrc/avr_bodies.h"
 #include "../avrecode-ms_b200/csrc/avr_host_tables.h"
 #include "../avrecode-ms_b200/csrc/avr_pipeline.h"
+#if defined(AVR_EMUL_SPEC)
+#include "../avrecode-ms_b200/csrc/avr_decode_spec.h"   // experimental warp-speculative chain (lanes emulated as a loop)
+#else
 #include "../avrecode-ms_b200/csrc/avr_decode.h"
+#endif
 #include "../avrecode-ms_b200/csrc/avr_parse.h"
 #include "../avrecode-ms_b200/csrc/avr_streams.h"
 #include <algorithm>

@@ -89,6 +89,21 @@ def test_device_parse_overflow_falls_back_to_host_recorder(ctx, monkeypatch):
         assert c == open(os.path.join(GOLDEN, n + ".avrec"), "rb").read(), n
 
 
+def test_experimental_speculative_chain_restores_the_same_files(ctx, tmpdir_path, monkeypatch):
+    """AVR_DEC_SPEC=1: the warp-speculative decompress kernel (avr_kernels_spec.cu; measured slower, not the product) gives back the
+    same bytes as the product chain, on the goldens (I/P/B, 8x8) and on generated clips with several slices per picture"""
+    import avr_ctypes as A
+    datas = [open(os.path.join(GOLDEN, n + ".h264"), "rb").read() for n in GOLDEN_NAMES]
+    datas += [gen_clip(os.path.join(tmpdir_path, f"s{i}.h264"), seed=170 + i, mb_w=11 + 3 * i, mb_h=6 + i, frames=5,
+                       slices_per_frame=1 + i, transform_8x8=i & 1, p_skip=60 + 60 * i) for i in range(3)]
+    comp, _ = A.compress_files(ctx, datas)
+    monkeypatch.setenv("AVR_DEC_SPEC", "1")
+    back, t = A.decompress_files(ctx, comp)
+    monkeypatch.delenv("AVR_DEC_SPEC")
+    assert back == datas
+    assert t["kernel_ms"] > 0
+
+
 def test_cli_recode_test_directory(ctx, tmpdir_path):
     """`recode test <dir>` (test.cpp): decompressed copies + metrics.csv with the reference's columns"""
     import shutil

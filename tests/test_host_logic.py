@@ -10,6 +10,7 @@ from conftest import GOLDEN, GOLDEN_NAMES, ROOT, gen_clip, have_ref, hex_payload
 
 EMUL = os.path.join(ROOT, "build", "avr_emul")
 EMUL_ASAN = os.path.join(ROOT, "build", "avr_emul_asan")
+EMUL_SPEC = os.path.join(ROOT, "build", "avr_emul_spec")
 
 
 def golden_payloads(name):
@@ -109,3 +110,13 @@ def test_repeated_frame_num_extended_and_strict_domain(tmpdir_path):
     for cmd in ("roundtrip", "parse"):
         rc, out, err = run([EMUL, cmd, clip])
         assert rc == 0 and out.startswith(b"OK"), out + err
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_speculative_chain_body_restores_original_cabac_bytes(name):
+    """the experimental warp-speculative decompress chain (avr_decode_spec.h, AVR_DEC_SPEC=1 on the device), 32 lanes emulated as
+    a loop: same roundtrip property as the product chain"""
+    if not os.path.exists(EMUL_SPEC):
+        pytest.skip("build/avr_emul_spec not built")
+    rc, out, err = run([EMUL_SPEC, "roundtrip", os.path.join(GOLDEN, name + ".h264")])
+    assert rc == 0 and out.startswith(b"OK"), out + err
