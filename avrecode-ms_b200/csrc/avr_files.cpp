@@ -369,8 +369,9 @@ static int compress_core(const std::vector<avr_context*>& lanes, const uint8_t* 
   avr_trace(nullptr);
   std::atomic<int> nomem(0);
   parallel_for(n, host_threads, [&](int f) {
-    // streams the device path does not cover (CAVLC, B/field/MBAFF, 4:2:2+, I_PCM, repeated frame_num)
-    // are stored whole as one literal block: a valid container that restores the input.
+    // what neither path could record (a launch limit, AVR_STRICT_DOMAIN with repeated frame_num) is stored whole as one literal
+    // block: a valid container that restores the input.  Slices outside the covered syntax (CAVLC, field/MBAFF, 4:2:2+, I_PCM,
+    // damaged data) are left literal one by one instead (avr_record.h slice_abort, scan_annexb_slices).
     if (!done[f] && rec_rc[f]) { containers[f].clear(); put_block_literal(containers[f], in[f], in_len[f]); }
     if (!to_buffer(containers[f], &out[f])) nomem = 1;
   });
@@ -437,6 +438,7 @@ static int decompress_core(const std::vector<avr_context*>& lanes, const uint8_t
     size_t next = 0;
     bool have = false; int w = 0, h = 0, fnum = 0;
     int nflips = 0; bool last_prev_valid = false;
+    int unsupported = 0;
     int rc = avr::scan_annexb_slices(d.surrogate.data(), d.surrogate.size(), [&](const avr::SliceLoc& loc) -> int {
       const avr::SliceHeaderInfo& sh = loc.sh;
       if (sh.sp.first_mb == 0 && !(avr::strict_domain() && have && sh.sp.mb_w == w && sh.sp.mb_h == h && sh.frame_num == fnum)) {   // update_frame_spec; every picture flips unless AVR_STRICT_DOMAIN (avr_record.h)
@@ -461,10 +463,12 @@ static int decompress_core(const std::vector<avr_context*>& lanes, const uint8_t
       s.sp.chroma_format_idc = sh.sp.chroma_format_idc; s.sp.direct_8x8_inference = sh.sp.direct_8x8_inference;
       d.slices.push_back(s); d.slice_block.push_back(coded_blk[next - 1]);
       return 0;
-    });
-    if (rc) { d.rc = rc; return; }
+    }, &unsupported);
+    // a container whose coded blocks belong to slices this library passes over (field/MBAFF, 4:2:2+ ... written by the reference's
+    // compressor) cannot line up with the scan: say unsupported rather than corrupt
+    if (rc) { d.rc = unsupported ? AVR_E_UNSUPPORTED : rc; return; }
     for (; next < coded_blk.size(); next++)
-      if (d.blocks[coded_blk[next]].has_cabac) { d.rc = AVR_E_CORRUPT; return; }   // "Not all blocks were decoded."
+      if (d.blocks[coded_blk[next]].has_cabac) { d.rc = unsupported ? AVR_E_UNSUPPORTED : AVR_E_CORRUPT; return; }   // "Not all blocks were decoded."
   });
   for (int f = 0; f < n; f++)
     if (files[f].rc) { avr_set_error("container %d: invalid (%d)", f, files[f].rc); return files[f].rc; }

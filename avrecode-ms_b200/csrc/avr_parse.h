@@ -345,6 +345,10 @@ AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uin
   AvrParsePolicy io;
   int rc;
   { avr::SliceParser<AvrParsePolicy, HAS_B> parser(io, ps.sp, row, 1); rc = parser.run(); }
+  // the walk must end on rbsp_stop_one_bit (avr_record.cpp record_annexb, cabac_std.h bits_consumed): bits in val count from the
+  // top, the 9-bit codIOffset window is read
+  const uint32_t consumed = 8u * g_par.pos - (uint32_t)g_par.nvalid + 9u;
+  if (rc >= 0 && (consumed + 6u) / 8u != ps.size) rc = avr::SYN_E_LENGTH;
   res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted;
   const int over = g_par.nb > g_par.bin_cap || g_par.nblk > g_par.blk_cap;
   res->status = over ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;

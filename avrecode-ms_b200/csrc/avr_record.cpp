@@ -51,7 +51,7 @@ static bool find_payload(const uint8_t* data, size_t n, size_t prev_coded_end, c
   return true;
 }
 
-int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice) {
+int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice, int* unsupported) {
   std::vector<Sps> sps(32);
   std::vector<Pps> pps(256);
   std::vector<uint8_t> rbsp;
@@ -74,8 +74,7 @@ int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(co
     const size_t bit_length = 8 * len - (size_t)r;
     SliceLoc loc;
     if (!parse_slice_header(rbsp.data(), bit_length, type, ref_idc, sps.data(), pps.data(), &loc.sh)) continue;
-    if (!loc.sh.cabac) return AVR_E_UNSUPPORTED;   // CAVLC: nothing to recode
-    if (!loc.sh.supported) return AVR_E_UNSUPPORTED;
+    if (!loc.sh.cabac || !loc.sh.supported) { if (unsupported) ++*unsupported; continue; }   // CAVLC: nothing to recode; syntax not covered
     const size_t start = (loc.sh.header_bits + 7) / 8;
     if (bit_length <= 8 * start) continue;
     loc.size = (bit_length - 8 * start + 7) / 8;
@@ -111,7 +110,7 @@ int scan_annexb(const uint8_t* data, size_t n, FileRecord* out, std::vector<Scan
     coded->push_back(s);
     rec.slice_end();
     return 0;
-  });
+  }, &out->skipped_slices);
   out->error = rc;
   return rc;
 }
@@ -130,6 +129,7 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
     if (loc.size >= 8 && loc.raw_off >= prev_coded_end) found = find_payload(data, n, prev_coded_end, loc, &found_at);
     rec.slice_begin(found, found ? found_at : loc.raw_off, (uint32_t)loc.size, sh.sp);
     if (!found) return 0;
+    const size_t prev_coded_end_before = prev_coded_end;
     prev_coded_end = found_at + loc.size;
     if ((int)row.size() < sh.sp.mb_w) { row.resize((size_t)sh.sp.mb_w); for (auto& m : row) m.uid = 0; }
     RecordIO io(rec);
@@ -137,10 +137,18 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
     cabac_init_states(io.st, sh.sp.slice_type == SLICE_I, sh.sp.cabac_init_idc, sh.sp.slice_qp);
     SliceParser<RecordIO> parser(io, sh.sp, row.data(), ++uid);
     int prc = parser.run();
+    // A walk that does not end on the last bit of slice_data() is not one the decompressor can reproduce (damaged data, syntax
+    // the template does not cover): for a conforming slice the last bit read is rbsp_stop_one_bit (cabac_std.h), which `size` of
+    // libavcodec's init_decoder call does not count.
+    if (prc >= 0 && (io.dec.bits_consumed() + 6) / 8 != loc.size) prc = SYN_E_LENGTH;
+    if (prc < 0) {                         // also I_PCM or a value out of range: this slice alone stays literal
+      rec.slice_abort();
+      prev_coded_end = prev_coded_end_before;
+      return 0;
+    }
     rec.slice_end();
-    if (prc < 0) return prc == SYN_E_PCM ? AVR_E_UNSUPPORTED : AVR_E_CORRUPT;
     return 0;
-  });
+  }, &out->skipped_slices);
   out->error = rc;
   return rc;
 }

@@ -33,6 +33,7 @@ struct FileRecord {
   int out_of_domain = 0;      // bit0: consecutive pictures share frame_num and AVR_STRICT_DOMAIN=1: not compressible (literal)
                               // bit1: they do, and the picture was given its own store (extended domain, see frame_spec)
   int error = 0;              // AVR_E_* from the parse
+  int skipped_slices = 0;     // slices left uncoded one by one: walk failed (slice_abort) or header outside the supported syntax
 };
 
 inline bool strict_domain() {
@@ -81,8 +82,24 @@ class Recorder {
       sl.bin_start = sl.bin_end = (uint32_t)r_->bins.size();
       sl.block_start = sl.block_end = (uint32_t)r_->blocks.size();
       r_->slices.push_back(sl);
+      mark_emitted_ = r_->emitted; mark_source_ = r_->source_bins;
     }
     in_sigmap_ = false;
+  }
+  // Per-slice fallback: the walk of the slice that slice_begin(coded = true) opened failed (I_PCM, a value out of range in a
+  // damaged slice).  Its records are dropped and its span becomes a skip_coded one (recode.cpp:1296-1303: the bytes stay in the
+  // literal, a size-only block keeps the block sequence aligned), so the model never sees the slice -- on decompress it is not
+  // walked either -- and the rest of the file is still coded.
+  void slice_abort() {
+    if (!coded_) return;
+    const AvrSlice sl = r_->slices.back();
+    r_->slices.pop_back();
+    r_->bins.resize(sl.bin_start);
+    r_->blocks.resize(sl.block_start);
+    r_->emitted = mark_emitted_; r_->source_bins = mark_source_;
+    r_->spans.back().slice_index = -1;
+    r_->skipped_slices++;
+    coded_ = false; in_sigmap_ = false;
   }
   void slice_end() {
     if (!coded_) return;
@@ -139,6 +156,7 @@ class Recorder {
   FILE* trace_;
   bool have_ = false; int w_ = 0, h_ = 0, frame_num_ = 0;
   bool coded_ = false, in_sigmap_ = false, expect_eob_ = false;
+  uint64_t mark_emitted_ = 0, mark_source_ = 0;
   uint32_t mb_addr_ = 0;
   int cat_ = 0, n_ = 0, max_coeff_ = 0, is_dc_ = 0, c422_ = 0;
 };
@@ -158,8 +176,10 @@ struct SliceLoc {
   size_t payload_avail = 0;    // unescaped bytes available from `payload` to the end of the NAL
 };
 // Walks the NALs, tracks SPS/PPS, calls on_slice for every CABAC slice with a non-empty payload.
-// Returns AVR_OK, the callback's non-zero result, or AVR_E_UNSUPPORTED (CAVLC / B / field / FMO / 4:2:2+).
-int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice);
+// Returns AVR_OK or the callback's non-zero result.
+// Slices whose header is outside the supported syntax (CAVLC, SP/SI, field/MBAFF, FMO, 4:2:2+, high bit depth) are passed over --
+// no callback, *unsupported counts them: they stay literal bytes and take no block of the container, on both directions alike.
+int scan_annexb_slices(const uint8_t* data, size_t n, const std::function<int(const SliceLoc&)>& on_slice, int* unsupported = nullptr);
 
 // One coded slice found by scan_annexb: what the device-side parse (avr_parse.h) needs.
 struct ScanSlice {

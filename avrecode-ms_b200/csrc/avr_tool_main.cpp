@@ -26,7 +26,7 @@ int main(int argc, char** argv) {
   avr::FileRecord rec;
   int rc = avr::record_annexb(data.data(), data.size(), &rec, cmd == "trace" ? stdout : nullptr);
   if (cmd == "stats" || rc != 0)
-    fprintf(stderr, "rc=%d bins=%zu blocks=%zu slices=%zu spans=%zu frames=%zu ood=%d\n", rc, rec.bins.size(),
-            rec.blocks.size(), rec.slices.size(), rec.spans.size(), rec.frames.size(), rec.out_of_domain);
+    fprintf(stderr, "rc=%d bins=%zu blocks=%zu slices=%zu spans=%zu frames=%zu ood=%d skipped=%d\n", rc, rec.bins.size(),
+            rec.blocks.size(), rec.slices.size(), rec.spans.size(), rec.frames.size(), rec.out_of_domain, rec.skipped_slices);
   return rc ? 1 : 0;
 }

@@ -34,7 +34,7 @@ inline void cabac_init_states(uint8_t* st /*[1024]*/, int slice_is_intra, int ca
 class CabacDecoder {
  public:
   void init(const uint8_t* buf, size_t size) {
-    p_ = buf; end_ = buf + size; bitbuf_ = 0; nbits_ = 0;
+    p_ = begin_ = buf; end_ = buf + size; bitbuf_ = 0; nbits_ = 0; over_ = 0;
     range_ = 510;
     offset_ = read_bits(9);
   }
@@ -78,16 +78,24 @@ class CabacDecoder {
   inline uint32_t read_bits(int n) {
     if (n == 0) return 0;
     while (nbits_ < n) {
-      uint32_t b = p_ < end_ ? *p_++ : 0;
+      uint32_t b = 0;
+      if (p_ < end_) b = *p_++; else over_++;
       bitbuf_ = (bitbuf_ << 8) | b;
       nbits_ += 8;
     }
     nbits_ -= n;
     return (uint32_t)((bitbuf_ >> nbits_) & ((1u << n) - 1));
   }
-  const uint8_t* p_ = nullptr; const uint8_t* end_ = nullptr;
+  const uint8_t* p_ = nullptr; const uint8_t* end_ = nullptr; const uint8_t* begin_ = nullptr;
   uint64_t bitbuf_ = 0; int nbits_ = 0;
+  size_t over_ = 0;            // zero bytes supplied past the end of the buffer
   uint32_t range_ = 510, offset_ = 0;
+
+ public:
+  // Bits the engine has read, the 9-bit codIOffset window included.  After end_of_slice_flag = 1 of a conforming slice this is
+  // the length of slice_data() plus one: the encoder's flush (9.3.4.5) ends with WriteBits(((low >> 7) & 3) | 1, 2), whose last
+  // bit is rbsp_stop_one_bit, and the window reaches exactly that far.
+  size_t bits_consumed() const { return ((size_t)(p_ - begin_) + over_) * 8 - (size_t)nbits_; }
 };
 
 // Textbook encoder (9.3.4.2 .. 9.3.4.5) writing into a byte vector.

@@ -36,7 +36,7 @@ enum { TERM_PCM = 0, TERM_EOS = 1 };
 enum { HINT_I16_PRED = 0, HINT_CHROMA_PRED, HINT_I4_PRED, HINT_REF_IDX, HINT_DQP };
 
 enum { SYN_OK = 0, SYN_E_PCM = -10, SYN_E_DQP = -11, SYN_E_REF = -12, SYN_E_SLICE_TYPE = -13,
-       SYN_E_MVD = -14 };
+       SYN_E_MVD = -14, SYN_E_LENGTH = -15 /* set by the callers: the walk did not end where slice_data() ends */ };
 
 struct SliceParams {
   int slice_type;        // SLICE_P / SLICE_I (slice_type % 5 mapped; SP/SI unsupported)

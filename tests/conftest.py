@@ -73,3 +73,36 @@ def golden_trace(name, td):
 def tmpdir_path():
     with tempfile.TemporaryDirectory() as td:
         yield td
+
+
+def damage_slice(data, which, seed=1, keep=12):
+    """overwrite the payload (all but the first `keep` bytes of the NAL) of the which-th slice NAL with bytes 0x10..0xFF: start codes,
+    NAL boundaries and the slice header stay, the CABAC data becomes noise"""
+    import random
+    import re
+    d = bytearray(data)
+    r = random.Random(seed)
+    idx = [m.start() for m in re.finditer(b"\x00\x00\x01", data)]
+    nals = []
+    for k, i in enumerate(idx):
+        s, e = i + 3, idx[k + 1] if k + 1 < len(idx) else len(d)
+        while e > s and d[e - 1] == 0:
+            e -= 1
+        nals.append((s, e))
+    s, e = [(s, e) for s, e in nals if d[s] & 31 in (1, 5)][which]
+    for i in range(s + keep, e - 1):
+        d[i] = r.randrange(0x10, 0x100)
+    return bytes(d)
+
+
+def as_cavlc(data):
+    """the same stream with entropy_coding_mode_flag = 0 in every PPS (pps_id = sps_id = 0: third bit of the PPS payload): its slices
+    are no longer CABAC slices for anyone who parses the headers"""
+    import re
+    d = bytearray(data)
+    for m in re.finditer(b"\x00\x00\x01", data):
+        h = m.start() + 3
+        if d[h] & 31 == 8:
+            assert d[h + 1] & 0xE0 == 0xE0, hex(d[h + 1])
+            d[h + 1] ^= 0x20
+    return bytes(d)

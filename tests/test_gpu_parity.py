@@ -104,6 +104,46 @@ def test_experimental_speculative_chain_restores_the_same_files(ctx, tmpdir_path
     assert t["kernel_ms"] > 0
 
 
+def test_per_slice_fallback_in_the_file_api(ctx):
+    """damaged slices and slices outside the supported syntax stay literal ONE BY ONE (skip_coded spans / no span), the rest of
+    the file is coded and every file comes back byte for byte; golden neighbours in the same batch are untouched"""
+    import avr_ctypes as A
+    from avrec_wire import parse_avrec
+    from conftest import as_cavlc, damage_slice
+    g = {n: open(os.path.join(GOLDEN, n + ".h264"), "rb").read() for n in GOLDEN_NAMES}
+    damaged = [damage_slice(g["multislice_multiref"], w, seed) for w, seed in ((1, 1), (5, 2), (11, 3))]
+    mixed = g["ip_basic"] + as_cavlc(g["skippy_idr"]) + g["b_slices"]
+    datas = [g["ip_basic"]] + damaged + [mixed, as_cavlc(g["dct8x8"]), g["multislice_multiref"]]
+    comp, _ = A.compress_files(ctx, datas)
+    assert comp[0] == open(os.path.join(GOLDEN, "ip_basic.avrec"), "rb").read()
+    assert comp[-1] == open(os.path.join(GOLDEN, "multislice_multiref.avrec"), "rb").read()
+    for c in comp[1:4]:                                           # 11 coded slices + one size-only block
+        blocks = parse_avrec(c)
+        assert sum(1 for b in blocks if "cabac" in b) == 11 and sum(1 for b in blocks if b.get("skip_coded")) == 1
+    blocks = parse_avrec(comp[4])
+    assert sum(1 for b in blocks if "cabac" in b) == 3 + 10       # ip_basic + b_slices; the CAVLC part takes no block
+    assert all("literal" in b for b in parse_avrec(comp[5]))      # nothing to code: literal only
+    assert len(comp[4]) < len(mixed)
+    back, _ = A.decompress_files(ctx, comp)
+    assert back == datas
+    # the device parse refuses exactly the damaged files (they go through the host recorder); everything else stays on the device
+    b = A.CBatch(ctx, files=datas)
+    assert [st != 0 for st in b.file_status] == [False, True, True, True, False, False, False], b.file_status
+    b.close()
+
+
+def test_device_parse_accepts_every_slice_of_generated_clips(ctx, tmpdir_path):
+    """the end-of-slice length check of the device parse (avr_parse.h) must not send a conforming file to the host recorder:
+    clips of the bench family (several sizes, 1-4 slices per picture, I/P/B, 8x8 on and off)"""
+    import avr_ctypes as A
+    datas = [gen_clip(os.path.join(tmpdir_path, f"v{i}.h264"), seed=900 + i, mb_w=8 + 5 * i, mb_h=6 + 3 * i, frames=3 + (i & 3),
+                      slices_per_frame=1 + i % 4, transform_8x8=(i >> 1) & 1, p_skip=30 * i, num_ref=1 + i % 3,
+                      **({"p_bslice": 500} if i % 3 == 2 else {})) for i in range(9)]
+    b = A.CBatch(ctx, files=datas)
+    assert not any(b.file_status), b.file_status
+    b.close()
+
+
 def test_cli_recode_test_directory(ctx, tmpdir_path):
     """`recode test <dir>` (test.cpp): decompressed copies + metrics.csv with the reference's columns"""
     import shutil

@@ -6,7 +6,7 @@ import os
 import pytest
 
 from avrec_wire import parse_avrec
-from conftest import GOLDEN, GOLDEN_NAMES, ROOT, gen_clip, have_ref, hex_payloads, oracle_encode, ref_trace, run
+from conftest import GOLDEN, GOLDEN_NAMES, ROOT, as_cavlc, damage_slice, gen_clip, have_ref, hex_payloads, oracle_encode, ref_trace, run
 
 EMUL = os.path.join(ROOT, "build", "avr_emul")
 EMUL_ASAN = os.path.join(ROOT, "build", "avr_emul_asan")
@@ -120,3 +120,39 @@ def test_speculative_chain_body_restores_original_cabac_bytes(name):
         pytest.skip("build/avr_emul_spec not built")
     rc, out, err = run([EMUL_SPEC, "roundtrip", os.path.join(GOLDEN, name + ".h264")])
     assert rc == 0 and out.startswith(b"OK"), out + err
+
+
+@pytest.mark.parametrize("which,seed", [(1, 1), (3, 2), (5, 3), (11, 4)])
+def test_damaged_slice_is_left_literal_and_the_rest_is_coded(which, seed, tmp_path):
+    """per-slice fallback (avr_record.h slice_abort): a slice whose walk does not end on rbsp_stop_one_bit becomes a skip_coded span
+    (reference container form recode.cpp:1296-1303), the other slices are recorded as before and the file round-trips through
+    the compress / decompress bodies"""
+    src = open(os.path.join(GOLDEN, "multislice_multiref.h264"), "rb").read()
+    bad = tmp_path / "damaged.h264"
+    bad.write_bytes(damage_slice(src, which, seed))
+    tool = os.path.join(ROOT, "avrecode-ms_b200", "bin", "avrtool")
+    rc, _, err = run([tool, "stats", str(bad)])
+    assert rc == 0 and b"slices=11 spans=12" in err and b"skipped=1" in err, err
+    rc, _, err = run([tool, "stats", os.path.join(GOLDEN, "multislice_multiref.h264")])
+    assert rc == 0 and b"slices=12 spans=12" in err and b"skipped=0" in err, err
+    rc, out, err = run([EMUL, "roundtrip", str(bad)])
+    assert rc == 0 and out.startswith(b"OK slices=11"), out + err
+    # the device parse body flags the slice (the file then goes through the host recorder, avr_files.cpp)
+    rc, out, err = run([EMUL, "parse", str(bad)])
+    assert rc != 0 and b"slice status -5" in out + err
+
+
+def test_slices_outside_the_supported_syntax_are_passed_over_one_by_one(tmp_path):
+    """a CABAC stream followed by a CAVLC one (new PPS): the first part is recorded, the slices of the second take no span at all
+    (scan_annexb_slices), instead of the whole file being refused"""
+    a = open(os.path.join(GOLDEN, "ip_basic.h264"), "rb").read()
+    b = as_cavlc(open(os.path.join(GOLDEN, "skippy_idr.h264"), "rb").read())
+    mixed = tmp_path / "mixed.h264"
+    mixed.write_bytes(a + b)
+    tool = os.path.join(ROOT, "avrecode-ms_b200", "bin", "avrtool")
+    rc, _, err = run([tool, "stats", str(mixed)])
+    assert rc == 0 and b"slices=3 spans=3" in err and b"skipped=10" in err, err
+    only = tmp_path / "cavlc.h264"
+    only.write_bytes(b)
+    rc, _, err = run([tool, "stats", str(only)])
+    assert rc == 0 and b"slices=0 spans=0" in err and b"skipped=10" in err, err
