@@ -757,7 +757,15 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   cudaEventRecord(ctx->ev[1], st);
   int has_b = 0;
   for (const AvrParseSlice& q : ps) if (q.sp.slice_type == avr::SLICE_B) has_b = 1;
-  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, d_order, has_b, st);
+  // slices longer than AVR_PARSE_LONG percent of the longest keep a warp to themselves (avr_k_parse)
+  uint32_t nlong = 0;
+  {
+    int pct = 35;
+    if (const char* e = getenv("AVR_PARSE_LONG")) { const int v = atoi(e); if (v >= 0 && v <= 100) pct = v; }
+    const uint64_t lim = ns ? (uint64_t)ps[order[0]].size * (uint64_t)pct / 100u : 0;
+    while (nlong < ns && ps[order[nlong]].size > lim) nlong++;
+  }
+  rc = avr_launch_parse(d_ps, ns, d_raw, d_bins, d_blkpool, d_rows, d_row_off, ctx->d_tab, d_res, d_order, nlong, has_b, st);
   cudaEventRecord(ctx->ev[2], st);
   if (rc) { avr_set_error("parse launch: %s", cudaGetErrorString((cudaError_t)rc)); return fail(AVR_E_CUDA); }
   std::vector<AvrParseResult> res(ns);

@@ -94,20 +94,25 @@ __global__ void __launch_bounds__(128) avr_k_patch_tails(const AvrParseSlice* ps
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s < n) avr_body_patch_tail(ps[s], raw);
 }
-// Compress-side parse on the device (avr_parse.h): one warp per coded slice, lane 0 walks the slice,
-// all lanes initialise the CABAC states and tables.
+// Compress-side parse on the device (avr_parse.h).  The launch order is longest payload first.  The first `nlong` slices get a warp
+// each (lane 0 walks the slice: a long slice sets the kernel's duration and must not wait for neighbours); the others are packed
+// `pack` to a warp, neighbours in the order and therefore of similar length, every lane walking its own slice on its own
+// AvrParShared: lanes that are at the same place of the syntax (same macroblock type, same block, same loop) issue together.
 template <bool HAS_B>
 __global__ void __launch_bounds__(32) avr_k_parse(const AvrParseSlice* ps, uint32_t n, const uint8_t* raw, uint16_t* bins_pool,
                                                   AvrBlock* blk_pool, avr::MbInfo* row_pool, const uint64_t* row_off,
-                                                  const AvrTables* tab, AvrParseResult* res, const uint32_t* order) {
+                                                  const AvrTables* tab, AvrParseResult* res, const uint32_t* order, uint32_t nlong,
+                                                  uint32_t pack) {
   const uint32_t lane = threadIdx.x;
-  if (blockIdx.x >= n) return;
-  const uint32_t s = order[blockIdx.x];        // longest payload first: the grid runs in several waves (32 slices per SM at a time)
+  uint32_t i;
+  if (blockIdx.x < nlong) { if (lane != 0) return; i = blockIdx.x; }
+  else { if (lane >= pack) return; i = nlong + (blockIdx.x - nlong) * pack + lane; }
+  if (i >= n) return;
+  const uint32_t s = order[i];
   const AvrParseSlice& p = ps[s];
-  avr_par_tables(tab, (int)lane, 32);
-  avr_cabac_init_states(g_par.st, tab, p.sp.slice_type == avr::SLICE_I, p.sp.cabac_init_idc, p.sp.slice_qp, (int)lane, 32);
-  __syncwarp();
-  if (lane == 0) avr_parse_slice<HAS_B>(p, raw, bins_pool, blk_pool, row_pool + row_off[s], &res[s]);
+  avr_par_tables(tab, 0, 1);
+  avr_cabac_init_states(g_par.st, tab, p.sp.slice_type == avr::SLICE_I, p.sp.cabac_init_idc, p.sp.slice_qp, 0, 1);
+  avr_parse_slice<HAS_B>(p, raw, bins_pool, blk_pool, row_pool + row_off[s], &res[s]);
 }
 // capacity block pool -> dense block array
 __global__ void __launch_bounds__(128) avr_k_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count,
@@ -340,19 +345,32 @@ int avr_launch_compress_pipeline(const AvrDevBatch& b, cudaStream_t st, int* lau
 
 int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
                      avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, const uint32_t* order,
-                     int has_b, cudaStream_t st) {
+                     uint32_t nlong, int has_b, cudaStream_t st) {
   if (n == 0) return 0;
   avr_k_patch_tails<<<(n + 127) / 128, 128, 0, st>>>(ps, n, raw);
-  // Registers allow 28 one-warp blocks per SM, but with that many walkers at different places of the syntax code the
-  // kernel waits for instruction fetch (ncu on the bench corpus: stall no_instruction 34 %, profiles/r01_summary.md).
-  // Unused dynamic shared memory caps the residency at 12 per SM when the grid is large enough to fill the SMs that
-  // deep anyway: 148 -> 138 ms on 9 537 slices (8 per SM: 137, 5 per SM: 184).
+  // AVR_PARSE_PACK = slices per warp behind the first `nlong` (1 = every slice its own warp, round 1's layout).  Sweep on the
+  // 2048-clip corpus (profiles/r02_parse_pack_sweep.txt, parse ms summed over the two concurrent launches): 505 unpacked, 392-428
+  // with 4 per warp, 405-452 with 6, 409-445 with 8 (511 when slices up to 45 % of the longest are packed), 620-690 with 16,
+  // 1400 with 32: lanes only issue together while they are at the same place of the syntax, and every packed lane costs 3 KB
+  // of shared memory, i.e. residency.
+  uint32_t pack = 4;
+  if (const char* e = getenv("AVR_PARSE_PACK")) { const int v = atoi(e); if (v >= 1 && v <= 32) pack = (uint32_t)v; }
+  if (nlong > n || pack == 1) nlong = n;
+  // Shared memory per block = one AvrParShared per packed lane.  With one-lane blocks only, registers would allow 28 blocks per
+  // SM, but with that many walkers at different places of the syntax code the kernel waits for instruction fetch (round 1:
+  // stall no_instruction 34 %); 16 KB per block caps the residency at 12 (148 -> 138 ms on 9 537 slices).
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const size_t dyn = n > (uint32_t)sms * 12u ? 16000 : 0;
-  if (has_b) avr_k_parse<true><<<n, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
-  else avr_k_parse<false><<<n, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order);
+  size_t dyn = (size_t)pack * AVR_PAR_STRIDE;
+  if (dyn < 16000 && n > (uint32_t)sms * 12u) dyn = 16000;
+  const uint32_t grid = nlong + (n - nlong + pack - 1) / pack;
+  if (dyn > 48 * 1024) {                       // per device: set on every such launch (multi-GPU callers share the process)
+    if (has_b) cudaFuncSetAttribute(avr_k_parse<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * (int)AVR_PAR_STRIDE);
+    else cudaFuncSetAttribute(avr_k_parse<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * (int)AVR_PAR_STRIDE);
+  }
+  if (has_b) avr_k_parse<true><<<grid, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order, nlong, pack);
+  else avr_k_parse<false><<<grid, 32, dyn, st>>>(ps, n, raw, bins_pool, blk_pool, row_pool, row_off, tab, res, order, nlong, pack);
   return (int)cudaGetLastError();
 }
 int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,

@@ -61,6 +61,6 @@ int avr_launch_decompress_chain_spec(const AvrDevDBatch& b, cudaStream_t st);   
 int avr_launch_compact(const uint8_t* scratch, const uint64_t* scratch_off, const uint32_t* len, uint64_t* out_off,
                        uint64_t* total, uint8_t* out, uint32_t n, cudaStream_t st);
 int avr_launch_parse(const AvrParseSlice* ps, uint32_t n, uint8_t* raw, uint16_t* bins_pool, AvrBlock* blk_pool,
-                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, const uint32_t* order, int has_b, cudaStream_t st);
+                     avr::MbInfo* row_pool, const uint64_t* row_off, const AvrTables* tab, AvrParseResult* res, const uint32_t* order, uint32_t nlong, int has_b, cudaStream_t st);
 int avr_launch_gather_blocks(const AvrBlock* pool, const AvrParseSlice* ps, const uint32_t* count, const uint32_t* dst_off,
                              AvrBlock* dst, uint32_t n, cudaStream_t st);

@@ -57,7 +57,15 @@ struct AvrParShared {
 #define AVR_P_OFF(member) ((avr_sptr)offsetof(AvrParShared, member))
 
 #if defined(__CUDACC__)
-__shared__ AvrParShared g_par;
+// One AvrParShared per LANE in dynamic shared memory (avr_k_parse: slices shorter than the batch's long ones are packed several to
+// a warp, each lane walking its own slice on its own instance).  The stride is 2 mod 32 words (the 64-bit table rows need 8-byte
+// alignment): lanes that touch the same member spread over 16 banks.
+#define AVR_PAR_STRIDE ((((uint32_t)sizeof(AvrParShared) + 127u) & ~127u) + 8u)
+extern __shared__ __align__(16) uint8_t avr_par_dyn[];
+static __device__ __forceinline__ AvrParShared* avr_par_self() {
+  return reinterpret_cast<AvrParShared*>(avr_par_dyn + threadIdx.x * AVR_PAR_STRIDE);
+}
+#define g_par (*avr_par_self())
 #define AVR_PAR_FN static __device__ __noinline__
 #define AVR_PAR_INL static __device__ __forceinline__
 #define AVR_PAR_M __device__ __forceinline__
