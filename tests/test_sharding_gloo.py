@@ -56,3 +56,48 @@ def test_two_rank_sharding_is_disjoint_and_aggregates():
     recs = [A.Record(b) for b in blobs]
     assert r["mb"] == pytest.approx(sum(len(b) for b in blobs) / 1e6)           # whole-job aggregate
     assert r["bins"] == sum(x.bins for x in recs)
+
+
+def _strong_worker(rank, world, port, total, out_dir):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import bench
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    # what bench.py's strong leg does: every rank computes the same greedy longest-first assignment and keeps its part
+    part = bench.lpt_assign([bench.clip_weight(i) for i in range(total)], world)
+    mine = [i for i in range(total) if part[i] == rank]
+    load = torch.tensor([float(sum(bench.clip_weight(i) for i in mine))], dtype=torch.float64)
+    loads = [torch.zeros_like(load) for _ in range(world)]
+    dist.all_gather(loads, load)
+    ids = torch.full((total,), -1, dtype=torch.int64)
+    ids[:len(mine)] = torch.tensor(mine, dtype=torch.int64)
+    allids = [torch.zeros_like(ids) for _ in range(world)]
+    dist.all_gather(allids, ids)
+    if rank == 0:
+        import json
+        json.dump(dict(loads=[x.item() for x in loads], ids=[[int(v) for v in a.tolist() if v >= 0] for a in allids]),
+                  open(os.path.join(out_dir, "s.json"), "w"))
+    dist.destroy_process_group()
+
+
+def test_strong_leg_assignment_is_a_balanced_partition_every_rank_agrees_on():
+    """bench.py `strong` (BASELINE configs[3]): N clips in total over the ranks, greedy longest-first by macroblocks
+    coded; no collective on the data path, every rank derives the same partition locally"""
+    import json
+    import torch.multiprocessing as mp
+    import bench
+    total = 41
+    with tempfile.TemporaryDirectory() as out:
+        mp.spawn(_strong_worker, args=(2, 29741, total, out), nprocs=2, join=True)
+        r = json.load(open(os.path.join(out, "s.json")))
+    assert sorted(r["ids"][0] + r["ids"][1]) == list(range(total))              # a partition: disjoint and complete
+    w = [bench.clip_weight(i) for i in range(total)]
+    assert r["loads"] == [float(sum(w[i] for i in part)) for part in r["ids"]]
+    # LPT guarantee: the loads differ by at most one item (the smallest assigned to the heavier rank)
+    heavy = max(range(2), key=lambda k: r["loads"][k])
+    assert abs(r["loads"][0] - r["loads"][1]) <= min(w[i] for i in r["ids"][heavy])
+    # determinism: the same call gives the same answer, and one rank gets everything when there is one rank
+    assert bench.lpt_assign(w, 2) == bench.lpt_assign(w, 2)
+    assert set(bench.lpt_assign(w, 1)) == {0}
