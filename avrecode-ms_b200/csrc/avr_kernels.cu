@@ -32,9 +32,26 @@ __global__ void __launch_bounds__(32) avr_k_compress_chain(const AvrFileDesc* fd
 // steps between slices: zeroing the picture stores on a flip, CABAC state initialisation, staging
 // the per-bin tables and the default-key estimators in shared memory.
 #define AVR_DEC_THREADS 64
-#if defined(AVR_SWAP_WARPS)
+// Which of the block's two warps is the chain.  A block's warps take consecutive hardware warp slots and a slot's scheduler
+// is slot % 4, so with the chain always on warp 0 every chain of an SM sits on two of its four schedulers and the sleeping
+// encoders on the other two (ncu, 2048 chains: 720 M instructions on the busiest scheduler against 354 M on the idlest).
+// That is the FASTER arrangement: -DAVR_MIX_WARPS (roles swapped in every other block by a hash of the block index, chains on
+// all four schedulers, each next to polling encoders) runs the 2048-clip corpus in 770 ms against 588 ms
+// (profiles/r02_ab_warp_roles.txt).
+#if defined(AVR_ROLE4)
+// experiment: four warps per block, the chain on one of warps 0..2 (hash of the block index), the encoder on warp 3, the others idle:
+// chains on three schedulers, encoders on the fourth
+#undef AVR_DEC_THREADS
+#define AVR_DEC_THREADS 128
+#define AVR_CHAIN_TID (32 * (int)(((blockIdx.x * 2654435761u) >> 15) % 3u))
+#define AVR_ENC_TID 96
+#elif defined(AVR_SWAP_WARPS)
 #define AVR_CHAIN_TID 32
 #define AVR_ENC_TID 0
+#elif defined(AVR_MIX_WARPS)
+#define AVR_CHAIN_TID (avr_block_swapped() ? 32 : 0)
+#define AVR_ENC_TID (avr_block_swapped() ? 0 : 32)
+static __device__ __forceinline__ bool avr_block_swapped() { return ((blockIdx.x * 2654435761u) >> 15) & 1u; }
 #else
 #define AVR_CHAIN_TID 0
 #define AVR_ENC_TID 32
