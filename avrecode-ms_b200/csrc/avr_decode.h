@@ -53,6 +53,10 @@ struct AvrDecShared {
   alignas(16) uint32_t ring[AVR_RING];         // (ctx << 1) | symbol, or AVR_RING_EMPTY; the consumer empties what it has read
   uint32_t ring_head, ring_tail_seen;          // producer side
   volatile uint32_t ring_tail;                 // consumer progress (back-pressure)
+#if defined(AVR_ENC_MBAR)
+  alignas(8) uint64_t mbar;                    // experiment: the encoder waits on an mbarrier (one arrival per record) instead of polling
+  uint32_t mbar_phase;
+#endif
   // range decoder (arithmetic_code.h:220-288)
   uint64_t low, range, w_cur, w_next;
   const uint8_t* in;
@@ -145,6 +149,24 @@ AVR_DEC_INL int avr_cab_consume(AvrCabRegs& c, uint32_t rec) {
 }
 
 // ---- ring -----------------------------------------------------------------------------------------
+#if defined(AVR_ENC_MBAR) && defined(__CUDACC__)
+// producer: one arrival per posted record completes a phase (expected count 1); release semantics order the record store before it
+AVR_DEC_INL void avr_mbar_arrive() {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(&g_dec.mbar);
+  asm volatile("{ .reg .b64 st; mbarrier.arrive.shared.b64 st, [%0]; }" ::"r"(a) : "memory");
+}
+// consumer: hardware-suspended wait for the phase of parity `ph` (returns after a time limit at the latest)
+AVR_DEC_INL bool avr_mbar_try_wait(uint32_t ph) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(&g_dec.mbar);
+  uint32_t ok;
+  asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared.b64 p, [%1], %2, %3; selp.u32 %0, 1, 0, p; }"
+               : "=r"(ok) : "r"(a), "r"(ph), "r"(2000u) : "memory");
+  return ok != 0;
+}
+#define AVR_MBAR_ARRIVE() avr_mbar_arrive()
+#else
+#define AVR_MBAR_ARRIVE() do {} while (0)
+#endif
 AVR_DEC_INL void avr_ring_post(uint32_t ctx, int symbol) {
 #if defined(__CUDACC__)
   const uint32_t head = g_dec.ring_head;
@@ -154,6 +176,7 @@ AVR_DEC_INL void avr_ring_post(uint32_t ctx, int symbol) {
     g_dec.ring_tail_seen = t;
   }
   reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (ctx << 1) | (uint32_t)symbol;
+  AVR_MBAR_ARRIVE();
   g_dec.ring_head = head + 1;
 #else
   avr_cab_consume(g_cab_host, (ctx << 1) | (uint32_t)symbol);
@@ -170,6 +193,7 @@ AVR_DEC_INL void avr_ring_post_r(uint32_t& head, uint32_t& tail_seen, uint32_t c
     tail_seen = t;
   }
   reinterpret_cast<volatile uint32_t*>(g_dec.ring)[head & (AVR_RING - 1)] = (ctx << 1) | (uint32_t)symbol;
+  AVR_MBAR_ARRIVE();
   head++;
 #else
   (void)tail_seen; head++;
@@ -214,16 +238,28 @@ static __device__ __noinline__ void avr_cab_encoder_thread(uint8_t* out, uint32_
   }
 #else
   volatile uint32_t* ring = reinterpret_cast<volatile uint32_t*>(g_dec.ring);
+#if defined(AVR_ENC_MBAR)
+  uint32_t mph = g_dec.mbar_phase;
+#endif
   for (;;) {
     const uint32_t slot = tail & (AVR_RING - 1);
     uint32_t rec = ring[slot];
+#if defined(AVR_ENC_MBAR)
+    // the slot is the truth; the barrier only parks the warp.  A phase missed while consuming makes one wait return at once or
+    // end on its time limit, never lose a record.
+    while (rec == AVR_RING_EMPTY) { if (avr_mbar_try_wait(mph)) mph ^= 1u; rec = ring[slot]; }
+#else
     while (rec == AVR_RING_EMPTY) { __nanosleep(AVR_ENC_SLEEP); rec = ring[slot]; }
+#endif
     ring[slot] = AVR_RING_EMPTY;       // before the tail moves: the producer reuses a slot only after it has seen the tail pass it
     tail++;
     if ((tail & 63) == 0) g_dec.ring_tail = tail;
     if (avr_cab_consume(c, rec)) break;
   }
   g_dec.ring_tail = tail;
+#if defined(AVR_ENC_MBAR)
+  g_dec.mbar_phase = mph;
+#endif
 #endif
   g_dec.cab_n = c.n; g_dec.cab_err = c.err;
 }
@@ -359,6 +395,7 @@ AVR_DEC_INL void avr_ring_reserve(uint32_t head, uint32_t& tail_seen, uint32_t n
 AVR_DEC_INL void avr_ring_store(avr_sptr s_ring, uint32_t slot, uint32_t rec) {
 #if defined(__CUDACC__)
   avr_s_st32(s_ring + ((slot & (AVR_RING - 1)) << 2), rec);
+  AVR_MBAR_ARRIVE();
 #else
   (void)s_ring; (void)slot;
   if (rec != AVR_RING_EMPTY) avr_cab_consume(g_cab_host, rec);

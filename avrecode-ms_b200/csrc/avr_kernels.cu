@@ -80,6 +80,10 @@ __global__ void __launch_bounds__(AVR_DEC_THREADS) avr_k_decompress_chain(
     uint8_t* s0 = store_pool + (size_t)fd.mb_base * AVR_MB_STRIDE;
     avr_dec_file_begin(est_pool + (size_t)f * AVR_KEY_COUNT, s0, s0 + (size_t)fd.max_mbs * AVR_MB_STRIDE);
     s_failed = 0;
+#if defined(AVR_ENC_MBAR)
+    asm volatile("mbarrier.init.shared.b64 [%0], 1;" ::"r"((uint32_t)__cvta_generic_to_shared(&g_dec.mbar)) : "memory");
+    g_dec.mbar_phase = 0;
+#endif
   }
   __syncthreads();
   uint32_t uid = 0;
