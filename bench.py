@@ -463,14 +463,16 @@ def main():
             s_bins, s_mb = sc.bins, sum(len(b) for b in sblobs) / 1e6
             sc.close()
             # the same clips end to end through the file API
-            barrier()
-            t0 = time.perf_counter()
-            comp_r, _ = A.compress_files(ctx, sblobs, host_threads, copy=False)
-            back_r, _ = A.decompress_files(ctx, comp_r.views, host_threads, copy=False)
-            torch.cuda.synchronize()
-            s_e2e = time.perf_counter() - t0
-            s_exact = all(v == b for v, b in zip(back_r.views, sblobs)) and s_bad == 0
-            comp_r.close(); back_r.close()
+            s_e2e, s_exact = 1e30, s_bad == 0
+            for _ in range(2):               # like the e2e leg above: best of two passes (the first one sizes the context's caches)
+                barrier()
+                t0 = time.perf_counter()
+                comp_r, _ = A.compress_files(ctx, sblobs, host_threads, copy=False)
+                back_r, _ = A.decompress_files(ctx, comp_r.views, host_threads, copy=False)
+                torch.cuda.synchronize()
+                s_e2e = min(s_e2e, time.perf_counter() - t0)
+                s_exact = s_exact and all(v == b for v, b in zip(back_r.views, sblobs))
+                comp_r.close(); back_r.close()
             (s_c, s_d, s_e2e_max) = allmax(sc_c / 2e3, sc_d / 2e3, s_e2e)
             (s_bins_all, s_mb_all, s_ok) = allsum(float(s_bins), s_mb, 1.0 if s_exact else 0.0)
             strong = {"workload": f"BASELINE configs[3]: {args.strong_clips} clips in total (same generator family, the frame counts of "
