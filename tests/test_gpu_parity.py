@@ -111,12 +111,17 @@ def test_per_slice_fallback_in_the_file_api(ctx):
     from avrec_wire import parse_avrec
     from conftest import as_cavlc, damage_slice
     g = {n: open(os.path.join(GOLDEN, n + ".h264"), "rb").read() for n in GOLDEN_NAMES}
-    damaged = [damage_slice(g["multislice_multiref"], w, seed) for w, seed in ((1, 1), (5, 2), (11, 3))]
+    # slices 0, 3, 6, 9 open a picture (first_mb = 0: the store flip happens at a slice that is then left literal)
+    damaged = [damage_slice(g["multislice_multiref"], w, seed) for w, seed in ((1, 1), (3, 2), (11, 3))]
     mixed = g["ip_basic"] + as_cavlc(g["skippy_idr"]) + g["b_slices"]
-    datas = [g["ip_basic"]] + damaged + [mixed, as_cavlc(g["dct8x8"]), g["multislice_multiref"]]
+    first = damage_slice(g["multislice_multiref"], 0, 4)          # the IDR's first slice
+    two = damage_slice(damage_slice(g["multislice_multiref"], 6, 5), 7, 6)   # two in a row, the first of them opening a picture
+    datas = [g["ip_basic"]] + damaged + [mixed, as_cavlc(g["dct8x8"]), g["multislice_multiref"], first, two]
     comp, _ = A.compress_files(ctx, datas)
     assert comp[0] == open(os.path.join(GOLDEN, "ip_basic.avrec"), "rb").read()
-    assert comp[-1] == open(os.path.join(GOLDEN, "multislice_multiref.avrec"), "rb").read()
+    assert comp[6] == open(os.path.join(GOLDEN, "multislice_multiref.avrec"), "rb").read()
+    assert sum(1 for b in parse_avrec(comp[7]) if b.get("skip_coded")) == 1
+    assert sum(1 for b in parse_avrec(comp[8]) if b.get("skip_coded")) == 2 and sum(1 for b in parse_avrec(comp[8]) if "cabac" in b) == 10
     for c in comp[1:4]:                                           # 11 coded slices + one size-only block
         blocks = parse_avrec(c)
         assert sum(1 for b in blocks if "cabac" in b) == 11 and sum(1 for b in blocks if b.get("skip_coded")) == 1
@@ -128,7 +133,7 @@ def test_per_slice_fallback_in_the_file_api(ctx):
     assert back == datas
     # the device parse refuses exactly the damaged files (they go through the host recorder); everything else stays on the device
     b = A.CBatch(ctx, files=datas)
-    assert [st != 0 for st in b.file_status] == [False, True, True, True, False, False, False], b.file_status
+    assert [st != 0 for st in b.file_status] == [False, True, True, True, False, False, False, True, True], b.file_status
     b.close()
 
 
