@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include "../avrecode-ms_b200/csrc/avr_record.h"
+#include "../avrecode-ms_b200/csrc/avr_container.h"
 #include "../avrecode-ms_b200/csrc/avr_bodies.h"
 #include "../avrecode-ms_b200/csrc/avr_host_tables.h"
 #include "../avrecode-ms_b200/csrc/avr_pipeline.h"
@@ -214,6 +215,58 @@ static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRec
 }
 
 // device-side parse body (avr_parse.h) on the host, slice by slice, against the host recorder
+// files <clip> [out.avrec]: the file-level host logic around the emulated bodies -- container written from the record and the
+// compress body's payloads (avr_container.h write_container, what avr_compress_files does around the device batch), then ONLY the
+// container is used: reader, surrogate scan, slice headers re-read from the literal bytes, picture flips, block matching
+// (plan_decompress), the decompress body per planned slice, and the output assembled with the last-byte patch (assemble).
+static int files_roundtrip(const std::vector<uint8_t>& data, const avr::FileRecord& rec, const AvrTables& tab, const char* save) {
+  Compressed c;
+  if (compress_chain(rec, tab, &c)) return 1;
+  avrc::Buf cont;
+  avrc::write_container(data.data(), data.size(), (uint32_t)rec.spans.size(),
+                        [&](uint32_t i, uint64_t* off, uint32_t* size, int32_t* idx) { *off = rec.spans[i].payload_off; *size = rec.spans[i].size; *idx = rec.spans[i].slice_index; },
+                        [&](uint32_t idx, const uint8_t** p, uint32_t* len) { *p = c.payloads[idx].data(); *len = (uint32_t)c.payloads[idx].size(); }, cont);
+  if (cont.bad) return 1;
+  if (save) { FILE* f = fopen(save, "wb"); if (!f) return 2; fwrite(cont.p, 1, cont.n, f); fclose(f); }
+  avrc::DFile d;
+  avrc::plan_decompress(cont.p, cont.n, &d);
+  if (d.rc) { printf("plan rc=%d\n", d.rc); return 1; }
+  if (d.slices.size() != c.payloads.size()) { printf("planned %zu slices, coded %zu\n", d.slices.size(), c.payloads.size()); return 1; }
+  AvrFileDesc fd; memset(&fd, 0, sizeof fd);
+  std::vector<AvrDecSlice> ds; std::vector<uint8_t> pool; uint64_t out_total = 0;
+  for (const avr_dslice& sl : d.slices) {
+    AvrDecSlice x; memset(&x, 0, sizeof x);
+    x.payload_off = pool.size(); x.payload_len = sl.payload_len;
+    pool.insert(pool.end(), sl.payload, sl.payload + sl.payload_len);
+    x.out_off = out_total; x.out_cap = sl.size + 64; out_total += x.out_cap;
+    x.flip = sl.flip;
+    x.sp.slice_type = sl.sp.slice_type; x.sp.first_mb = sl.sp.first_mb; x.sp.mb_w = sl.sp.mb_w; x.sp.mb_h = sl.sp.mb_h;
+    x.sp.num_ref[0] = sl.sp.num_ref[0]; x.sp.num_ref[1] = sl.sp.num_ref[1]; x.sp.cabac_init_idc = sl.sp.cabac_init_idc;
+    x.sp.slice_qp = sl.sp.slice_qp; x.sp.transform_8x8_mode = sl.sp.transform_8x8_mode; x.sp.chroma_format_idc = sl.sp.chroma_format_idc;
+    x.sp.direct_8x8_inference = sl.sp.direct_8x8_inference;
+    if ((uint32_t)sl.sp.mb_w * (uint32_t)sl.sp.mb_h > fd.max_mbs) fd.max_mbs = (uint32_t)sl.sp.mb_w * (uint32_t)sl.sp.mb_h;
+    ds.push_back(x);
+  }
+  fd.nslices = (uint32_t)ds.size();
+  std::vector<uint16_t> est(AVR_KEY_COUNT, AVR_EST_INIT);
+  std::vector<uint8_t> s0((size_t)fd.max_mbs * AVR_MB_STRIDE + 16), s1(s0.size()), out(out_total + 16);
+  std::vector<avr::MbInfo> row(4096);
+  std::vector<uint32_t> olen(ds.size()), obins(ds.size());
+  std::vector<int> status(ds.size());
+  pool.resize(pool.size() + 16);
+  if (!ds.empty())
+    avr_decompress_file_host(fd, ds.data(), pool.data(), est.data(), s0.data(), s1.data(), row.data(), &tab, out.data(), olen.data(),
+                             obins.data(), status.data());
+  for (size_t k = 0; k < ds.size(); k++) if (status[k]) { printf("slice %zu: status %d\n", k, status[k]); return 1; }
+  uint8_t* back = nullptr; size_t back_n = 0;
+  if (!avrc::assemble(d, [&](uint32_t k, const uint8_t** p, uint32_t* len) { *p = out.data() + ds[k].out_off; *len = olen[k]; }, &back, &back_n)) return 2;
+  const bool same = back_n == data.size() && memcmp(back, data.data(), back_n) == 0;
+  free(back);
+  size_t nskip = 0; for (auto& b : d.blocks) nskip += b.has_skip;
+  printf("%s container=%zu bytes of %zu, blocks=%zu coded=%zu skip_coded=%zu\n", same ? "OK" : "FAIL", cont.n, data.size(), d.blocks.size(), ds.size(), nskip);
+  return same ? 0 : 1;
+}
+
 static int parse_check(const std::vector<uint8_t>& data, const avr::FileRecord& want, const AvrTables& tab, uint32_t fuzz_seed = 0, int fuzz_flips = 0) {
   avr::FileRecord scan;
   std::vector<avr::ScanSlice> coded;
@@ -339,6 +392,7 @@ int main(int argc, char** argv) {
     if (compress_pipeline(recs, tab, &all)) return 1;
     c = all.back();
   }
+  if (cmd == "files") return files_roundtrip(data, rec, tab, argc > 3 ? argv[3] : nullptr);
   if (cmd == "parse") return parse_check(data, rec, tab);
   if (cmd == "roundtrip") return decompress_check(data, rec, tab, c) ? 1 : 0;
   for (auto& p : c.payloads) print_hex("P ", p.data(), p.size());

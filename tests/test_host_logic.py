@@ -156,3 +156,36 @@ def test_slices_outside_the_supported_syntax_are_passed_over_one_by_one(tmp_path
     only.write_bytes(b)
     rc, _, err = run([tool, "stats", str(only)])
     assert rc == 0 and b"slices=0 spans=0" in err and b"skipped=10" in err, err
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_file_level_host_logic_writes_the_reference_container_and_inverts_it(name, tmp_path):
+    """avr_container.h (what avr_compress_files / avr_decompress_files do around the device batches) on the CPU: the container
+    written from the recorder's spans and the compress body's payloads is the reference compressor's .avrec byte for byte, and
+    from the container ALONE (reader, surrogate scan, slice headers re-read from the literal bytes, picture flips, block matching,
+    decompress body, last-byte patch) the input file comes back"""
+    out = tmp_path / (name + ".avrec")
+    rc, o, err = run([EMUL, "files", os.path.join(GOLDEN, name + ".h264"), str(out)])
+    assert rc == 0 and o.startswith(b"OK"), o + err
+    assert out.read_bytes() == open(os.path.join(GOLDEN, name + ".avrec"), "rb").read()
+
+
+def test_file_level_host_logic_on_fallback_and_degenerate_inputs(tmp_path):
+    """skip_coded blocks (damaged slices, also ones that open a picture: the store flip then belongs to the next coded slice), slices
+    passed over (CAVLC part between two CABAC parts), files without any coded slice, junk, the empty file"""
+    g = {n: open(os.path.join(GOLDEN, n + ".h264"), "rb").read() for n in GOLDEN_NAMES}
+    m = g["multislice_multiref"]
+    cases = {
+        "first": (damage_slice(m, 0, 4), b"coded=11 skip_coded=1"),
+        "opens_picture": (damage_slice(m, 3, 2), b"coded=11 skip_coded=1"),
+        "two_in_a_row": (damage_slice(damage_slice(m, 6, 5), 7, 6), b"coded=10 skip_coded=2"),
+        "mixed": (g["ip_basic"] + as_cavlc(g["skippy_idr"]) + g["b_slices"], b"coded=13 skip_coded=0"),
+        "cavlc_only": (as_cavlc(g["dct8x8"]), b"blocks=1 coded=0"),
+        "junk": (bytes(range(256)) * 3, b"blocks=1 coded=0"),
+        "empty": (b"", b"coded=0"),
+    }
+    for name, (data, want) in cases.items():
+        src = tmp_path / (name + ".h264")
+        src.write_bytes(data)
+        rc, o, err = run([EMUL_ASAN, "files", str(src)])
+        assert rc == 0 and o.startswith(b"OK") and want in o, (name, o, err)
