@@ -65,9 +65,16 @@ def test_bodies_match_oracle_on_fresh_clips(params, tmpdir_path):
         rc, out, err = run([EMUL, mode, clip])
         assert rc == 0, err
         assert hex_payloads(out) == want, mode
-    for cmd in ("roundtrip", "parse"):
+    for cmd in ("roundtrip", "parse", "files"):
         rc, out, err = run([EMUL, cmd, clip])
         assert rc == 0 and out.startswith(b"OK"), out + err
+    # the container written around the compress body == the live reference compressor's
+    if have_ref():
+        ours, theirs = os.path.join(tmpdir_path, "ours.avrec"), os.path.join(tmpdir_path, "ref.avrec")
+        assert run([EMUL, "files", clip, ours])[0] == 0
+        rc, _, err = run([os.path.join(ROOT, "oracle", "_ref", "recode"), "compress", clip, theirs])
+        assert rc == 0, err
+        assert open(ours, "rb").read() == open(theirs, "rb").read()
 
 
 @pytest.mark.parametrize("cmd", ["fuzzdec", "fuzzparse"])
