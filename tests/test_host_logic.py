@@ -114,7 +114,7 @@ def test_repeated_frame_num_extended_and_strict_domain(tmpdir_path):
     assert rc == 0 and b"ood=2" in err, err
     rc, _, err = run([tool, "stats", clip], env=dict(os.environ, AVR_STRICT_DOMAIN="1"))
     assert b"ood=1" in err, err
-    for cmd in ("roundtrip", "parse"):
+    for cmd in ("roundtrip", "parse", "files"):      # files: the decompress-side scan applies the same every-picture-flips rule
         rc, out, err = run([EMUL, cmd, clip])
         assert rc == 0 and out.startswith(b"OK"), out + err
 
