@@ -196,3 +196,26 @@ def test_file_level_host_logic_on_fallback_and_degenerate_inputs(tmp_path):
         src.write_bytes(data)
         rc, o, err = run([EMUL_ASAN, "files", str(src)])
         assert rc == 0 and o.startswith(b"OK") and want in o, (name, o, err)
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built")
+def test_random_clips_file_level_against_the_live_reference(tmpdir_path):
+    """a short run of tools/cpu_sweep.py (100 clips by hand: 0 differences): random geometry, slice counts, I/P/B mix, 8x8, skip
+    and coefficient densities; the container equals the reference compressor's and the file comes back from it"""
+    import random
+    rnd = random.Random(20261105)
+    ref = os.path.join(ROOT, "oracle", "_ref", "recode")
+    for i in range(10):
+        p = dict(seed=rnd.randrange(1, 10 ** 6), mb_w=rnd.randrange(2, 20), mb_h=rnd.randrange(2, 12), frames=rnd.randrange(1, 6),
+                 slices_per_frame=rnd.randrange(1, 5), transform_8x8=rnd.randrange(2), num_ref=rnd.randrange(1, 5),
+                 p_skip=rnd.choice([0, 60, 200, 250]), qp=rnd.randrange(10, 45), cabac_init_idc=rnd.randrange(3))
+        if rnd.random() < 0.5:
+            p.update(p_bslice=rnd.choice([100, 200, 240]), p_direct=rnd.choice([0, 80, 200]))
+        clip = os.path.join(tmpdir_path, f"r{i}.h264")
+        gen_clip(clip, **p)
+        ours, theirs = clip + ".ours", clip + ".ref"
+        rc, out, err = run([EMUL, "files", clip, ours])
+        assert rc == 0 and out.startswith(b"OK"), (p, out, err)
+        rc, _, err = run([ref, "compress", clip, theirs])
+        assert rc == 0, (p, err)
+        assert open(ours, "rb").read() == open(theirs, "rb").read(), p
