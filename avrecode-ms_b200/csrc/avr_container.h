@@ -153,10 +153,14 @@ inline void plan_decompress(const uint8_t* in, size_t in_len, DFile* out) {
   size_t next = 0;
   bool have = false; int w = 0, h = 0, fnum = 0;
   int nflips = 0; bool last_prev_valid = false;
-  int unsupported = 0;
+  int unsupported = 0, last_first_mb = -1;
   int rc = avr::scan_annexb_slices(d.surrogate.data(), d.surrogate.size(), [&](const avr::SliceLoc& loc) -> int {
     const avr::SliceHeaderInfo& sh = loc.sh;
-    if (sh.sp.first_mb == 0 && !(avr::strict_domain() && have && sh.sp.mb_w == w && sh.sp.mb_h == h && sh.frame_num == fnum)) {   // update_frame_spec; every picture flips unless AVR_STRICT_DOMAIN (avr_record.h)
+    // update_frame_spec; every picture flips unless AVR_STRICT_DOMAIN; a slice also starts a picture when none has started yet
+    // or the size changed under it or first_mb does not advance (avr_record.h starts_picture: the same rule on the compress side)
+    const bool starts_picture = sh.sp.first_mb == 0 || !have || sh.sp.mb_w != w || sh.sp.mb_h != h || sh.sp.first_mb <= last_first_mb;
+    last_first_mb = sh.sp.first_mb;
+    if (starts_picture && !(avr::strict_domain() && have && sh.sp.mb_w == w && sh.sp.mb_h == h && sh.frame_num == fnum)) {
       last_prev_valid = have && sh.sp.mb_w == w && sh.sp.mb_h == h;
       nflips++;
       have = true; w = sh.sp.mb_w; h = sh.sp.mb_h; fnum = sh.frame_num;

@@ -96,7 +96,7 @@ int scan_annexb(const uint8_t* data, size_t n, FileRecord* out, std::vector<Scan
   size_t prev_coded_end = 0;
   int rc = scan_annexb_slices(data, n, [&](const SliceLoc& loc) -> int {
     const SliceHeaderInfo& sh = loc.sh;
-    if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);
+    if (rec.starts_picture(sh.sp.first_mb, sh.sp.mb_w, sh.sp.mb_h)) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);
     bool found = false;
     size_t found_at = 0;
     if (loc.size >= 8 && loc.raw_off >= prev_coded_end) found = find_payload(data, n, prev_coded_end, loc, &found_at);
@@ -122,7 +122,7 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
   size_t prev_coded_end = 0;
   int rc = scan_annexb_slices(data, n, [&](const SliceLoc& loc) -> int {
     const SliceHeaderInfo& sh = loc.sh;
-    if (sh.sp.first_mb == 0) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);  // h264_frame_start
+    if (rec.starts_picture(sh.sp.first_mb, sh.sp.mb_w, sh.sp.mb_h)) rec.frame_spec(sh.frame_num, sh.sp.mb_w, sh.sp.mb_h);  // h264_frame_start
     // recode.cpp:1283-1286: memmem of the unescaped payload in the not-yet-emitted original bytes
     bool found = false;
     size_t found_at = 0;

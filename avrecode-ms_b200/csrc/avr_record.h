@@ -65,6 +65,17 @@ class Recorder {
     have_ = true; w_ = mb_w; h_ = mb_h; frame_num_ = frame_num;
   }
   uint32_t cur_frame() const { return r_->frames.empty() ? 0u : (uint32_t)r_->frames.size() - 1; }
+  // A slice starts a picture when it is the picture's first (first_mb == 0), and also when no picture has been started yet, when the
+  // picture size has changed under it, or when its first_mb does not lie beyond the previous slice's (CABAC profiles have no
+  // arbitrary slice order, so that slice belongs to a NEW picture whose first slice is missing or was refused).  Streams cut in
+  // the middle of a picture or with lost slices then never leave a slice without a picture store of its size, and never code a
+  // macroblock position twice into one store -- the slice-parallel compress passes rely on every position being visited once.
+  // avr_container.h plan_decompress applies the same rule from the same header fields.
+  bool starts_picture(int first_mb, int mb_w, int mb_h) {
+    const bool yes = first_mb == 0 || !have_ || mb_w != w_ || mb_h != h_ || first_mb <= last_first_mb_;
+    last_first_mb_ = first_mb;
+    return yes;
+  }
 
   // CABACCodingHooks::init_decoder. coded=false is the skip_coded path (hooks disabled).
   void slice_begin(bool coded, uint64_t payload_off, uint32_t size, const SliceParams& sp) {
@@ -154,7 +165,7 @@ class Recorder {
  private:
   FileRecord* r_;
   FILE* trace_;
-  bool have_ = false; int w_ = 0, h_ = 0, frame_num_ = 0;
+  bool have_ = false; int w_ = 0, h_ = 0, frame_num_ = 0, last_first_mb_ = -1;
   bool coded_ = false, in_sigmap_ = false, expect_eob_ = false;
   uint64_t mark_emitted_ = 0, mark_source_ = 0;
   uint32_t mb_addr_ = 0;

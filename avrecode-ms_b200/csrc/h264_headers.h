@@ -279,7 +279,9 @@ static inline bool parse_slice_header(const uint8_t* rbsp, size_t nbits, int nal
   if (pps.deblocking_control) {
     if (br.ue() != 1) { br.se(); br.se(); }
   }
-  if (br.err() || cabac_init_idc > 2u || qp < -64 || qp > 128) return false;
+  // SliceQPY outside 0..51 (8-bit video): libavcodec refuses the slice header (h264_slice.c "QP %u out of range"), so no hook
+  // ever sees the slice and the reference's container has no block for it
+  if (br.err() || cabac_init_idc > 2u || qp < 0 || qp > 51) return false;
   h.header_bits = br.pos();
   h.sp.slice_type = st;
   h.sp.first_mb = first_mb;

@@ -106,3 +106,15 @@ def as_cavlc(data):
             assert d[h + 1] & 0xE0 == 0xE0, hex(d[h + 1])
             d[h + 1] ^= 0x20
     return bytes(d)
+
+
+def drop_slice_nal(data, which_slice):
+    """the stream without its which_slice-th slice NAL (start code included)"""
+    import re
+    idx = [m.start() for m in re.finditer(b"\x00\x00\x01", data)]
+    k = [i for i in idx if data[i + 3] & 31 in (1, 5)][which_slice]
+    nxt = [i for i in idx if i > k]
+    end = nxt[0] if nxt else len(data)
+    while end > k and data[end - 1] == 0 and end - 1 > k + 3:       # the zero_byte of a 4-byte start code belongs to the next NAL
+        end -= 1
+    return data[:k] + data[end:]

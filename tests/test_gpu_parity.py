@@ -137,6 +137,23 @@ def test_per_slice_fallback_in_the_file_api(ctx):
     b.close()
 
 
+def test_streams_that_begin_in_the_middle_of_a_picture(ctx, tmpdir_path):
+    """no first_mb = 0 slice before the first coded slice (a cut stream; a first slice with a refused header, here QP out of range):
+    the first slice seen starts the picture on both directions -- no slice is left without a picture store of its size"""
+    import avr_ctypes as A
+    from conftest import drop_slice_nal
+    src = open(os.path.join(GOLDEN, "multislice_multiref.h264"), "rb").read()
+    datas = [drop_slice_nal(src, 0), drop_slice_nal(src, 3), drop_slice_nal(drop_slice_nal(src, 0), 0)]
+    datas += [gen_clip(os.path.join(tmpdir_path, f"q{qp}.h264"), seed=5, mb_w=8, mb_h=6, frames=3, slices_per_frame=2, num_ref=2, qp=qp)
+              for qp in (0, 51)]
+    datas.append(open(os.path.join(GOLDEN, "ip_basic.h264"), "rb").read())
+    comp, _ = A.compress_files(ctx, datas)
+    assert comp[-1] == open(os.path.join(GOLDEN, "ip_basic.avrec"), "rb").read()
+    assert all(len(c) < len(d) + 64 for c, d in zip(comp, datas))
+    back, _ = A.decompress_files(ctx, comp)
+    assert back == datas
+
+
 def test_device_parse_accepts_every_slice_of_generated_clips(ctx, tmpdir_path):
     """the end-of-slice length check of the device parse (avr_parse.h) must not send a conforming file to the host recorder:
     clips of the bench family (several sizes, 1-4 slices per picture, I/P/B, 8x8 on and off)"""

@@ -6,7 +6,7 @@ import os
 import pytest
 
 from avrec_wire import parse_avrec
-from conftest import GOLDEN, GOLDEN_NAMES, ROOT, as_cavlc, damage_slice, gen_clip, have_ref, hex_payloads, oracle_encode, ref_trace, run
+from conftest import GOLDEN, GOLDEN_NAMES, ROOT, as_cavlc, damage_slice, drop_slice_nal, gen_clip, have_ref, hex_payloads, oracle_encode, ref_trace, run
 
 EMUL = os.path.join(ROOT, "build", "avr_emul")
 EMUL_ASAN = os.path.join(ROOT, "build", "avr_emul_asan")
@@ -219,3 +219,40 @@ def test_random_clips_file_level_against_the_live_reference(tmpdir_path):
         rc, _, err = run([ref, "compress", clip, theirs])
         assert rc == 0, (p, err)
         assert open(ours, "rb").read() == open(theirs, "rb").read(), p
+
+
+def test_stream_that_begins_in_the_middle_of_a_picture(tmp_path):
+    """no slice with first_mb = 0 before the first coded slice (a cut stream, or a first slice whose header is refused): the first
+    slice seen starts the picture on both directions (avr_record.h starts_picture, avr_container.h plan_decompress) instead of
+    leaving coded slices without a picture store"""
+    tool = os.path.join(ROOT, "avrecode-ms_b200", "bin", "avrtool")
+    src = open(os.path.join(GOLDEN, "multislice_multiref.h264"), "rb").read()
+    # the IDR's first slice missing: its second slice starts the picture; the first slice of the second picture missing: that
+    # picture's second slice starts it (its first_mb does not lie beyond the previous slice's)
+    for drop, frames in ((0, b"frames=4"), (3, b"frames=4")):
+        clip = tmp_path / f"cut{drop}.h264"
+        clip.write_bytes(drop_slice_nal(src, drop))
+        rc, _, err = run([tool, "stats", str(clip)])
+        assert rc == 0 and b"slices=11" in err and frames in err, err
+        for cmd in ("roundtrip", "parse", "files"):
+            rc, out, err = run([EMUL_ASAN, cmd, str(clip)])
+            assert rc == 0 and out.startswith(b"OK"), (drop, cmd, out, err)
+        # every macroblock position is coded once per picture store: the slice-parallel passes agree with the sequential chain
+        assert run([EMUL, "chain", str(clip)])[1] == run([EMUL, "pipeline", str(clip)])[1]
+
+
+def test_slice_qp_out_of_range_is_refused_like_libavcodec_does(tmpdir_path):
+    """SliceQPY outside 0..51: libavcodec's slice header parse fails (no hook sees the slice, the reference writes no block for it);
+    the generator's per-slice QP variation around qp=0 / qp=51 produces such headers"""
+    tool = os.path.join(ROOT, "avrecode-ms_b200", "bin", "avrtool")
+    refused = 0
+    for qp in (0, 51):
+        clip = os.path.join(tmpdir_path, f"q{qp}.h264")
+        gen_clip(clip, seed=5, mb_w=8, mb_h=6, frames=3, slices_per_frame=2, num_ref=2, qp=qp)
+        rc, _, err = run([tool, "stats", clip])
+        assert rc == 0, err
+        refused += b"slices=6" not in err
+        for cmd in ("roundtrip", "parse", "files"):
+            rc, out, err = run([EMUL, cmd, clip])
+            assert rc == 0 and out.startswith(b"OK"), (qp, cmd, out, err)
+    assert refused, "the generator no longer produces out-of-range slice QPs: pick other parameters"
