@@ -357,6 +357,9 @@ AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uin
   // top, the 9-bit codIOffset window is read
   const uint32_t consumed = 8u * g_par.pos - (uint32_t)g_par.nvalid + 9u;
   if (rc >= 0 && (consumed + 6u) / 8u != ps.size) rc = avr::SYN_E_LENGTH;
+  // ... and through end_of_slice_flag = 1, not by running out of macroblocks: the decompress chain could not close such a slice
+  if (rc >= 0 && g_par.nb >= 1 && g_par.nb <= g_par.bin_cap && g_par.bins[g_par.nb - 1] != AVR_BIN(1, AVR_CTX_TERMINATE, AVR_KIND_DEFAULT))
+    rc = avr::SYN_E_LENGTH;
   res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted;
   const int over = g_par.nb > g_par.bin_cap || g_par.nblk > g_par.blk_cap;
   res->status = over ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;

@@ -141,6 +141,9 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
     // the template does not cover): for a conforming slice the last bit read is rbsp_stop_one_bit (cabac_std.h), which `size` of
     // libavcodec's init_decoder call does not count.
     if (prc >= 0 && (io.dec.bits_consumed() + 6) / 8 != loc.size) prc = SYN_E_LENGTH;
+    // ... and through end_of_slice_flag = 1, not by running out of macroblocks (a damaged last macroblock can end on the right
+    // bit with the flag read as 0): the decompress chain could not close such a slice
+    if (prc >= 0 && (out->bins.empty() || out->bins.back() != AVR_BIN(1, AVR_CTX_TERMINATE, AVR_KIND_DEFAULT))) prc = SYN_E_LENGTH;
     if (prc < 0) {                         // also I_PCM or a value out of range: this slice alone stays literal
       rec.slice_abort();
       prev_coded_end = prev_coded_end_before;
