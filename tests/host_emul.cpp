@@ -219,7 +219,8 @@ static int decompress_check(const std::vector<uint8_t>& data, const avr::FileRec
 // compress body's payloads (avr_container.h write_container, what avr_compress_files does around the device batch), then ONLY the
 // container is used: reader, surrogate scan, slice headers re-read from the literal bytes, picture flips, block matching
 // (plan_decompress), the decompress body per planned slice, and the output assembled with the last-byte patch (assemble).
-static int files_roundtrip(const std::vector<uint8_t>& data, const avr::FileRecord& rec, const AvrTables& tab, const char* save) {
+static int files_roundtrip(const std::vector<uint8_t>& data, const avr::FileRecord& rec, const AvrTables& tab, const char* save,
+                           uint32_t fuzz_seed = 0, int fuzz_flips = 0) {
   Compressed c;
   if (compress_chain(rec, tab, &c)) return 1;
   avrc::Buf cont;
@@ -228,10 +229,24 @@ static int files_roundtrip(const std::vector<uint8_t>& data, const avr::FileReco
                         [&](uint32_t idx, const uint8_t** p, uint32_t* len) { *p = c.payloads[idx].data(); *len = (uint32_t)c.payloads[idx].size(); }, cont);
   if (cont.bad) return 1;
   if (save) { FILE* f = fopen(save, "wb"); if (!f) return 2; fwrite(cont.p, 1, cont.n, f); fclose(f); }
+  // filesfuzz: bit flips in the CONTAINER (what avr_decompress_files gets from outside): reader, plan and chain must end with a
+  // status or a wrong file, inside their buffers (run under ASan); an exact-size heap copy makes any over-read visible
+  std::vector<uint8_t> exact(cont.p, cont.p + cont.n);
+  if (fuzz_flips) {
+    uint32_t x = fuzz_seed * 2654435761u + 777u;
+    for (int k = 0; k < fuzz_flips && !exact.empty(); k++) {
+      x = x * 1664525u + 1013904223u; const size_t pos = (x >> 8) % exact.size();
+      x = x * 1664525u + 1013904223u; exact[pos] ^= (uint8_t)(1u << ((x >> 13) & 7));
+    }
+  }
   avrc::DFile d;
-  avrc::plan_decompress(cont.p, cont.n, &d);
+  avrc::plan_decompress(exact.data(), exact.size(), &d);
+  if (fuzz_flips) {
+    size_t total = 0; for (auto& b : d.blocks) total += b.has_cabac ? (size_t)b.size : 0;
+    if (d.rc || total > (64u << 20)) { printf("TERMINATED plan rc=%d\n", d.rc); return 0; }
+  }
   if (d.rc) { printf("plan rc=%d\n", d.rc); return 1; }
-  if (d.slices.size() != c.payloads.size()) { printf("planned %zu slices, coded %zu\n", d.slices.size(), c.payloads.size()); return 1; }
+  if (!fuzz_flips && d.slices.size() != c.payloads.size()) { printf("planned %zu slices, coded %zu\n", d.slices.size(), c.payloads.size()); return 1; }
   AvrFileDesc fd; memset(&fd, 0, sizeof fd);
   std::vector<AvrDecSlice> ds; std::vector<uint8_t> pool; uint64_t out_total = 0;
   for (const avr_dslice& sl : d.slices) {
@@ -257,12 +272,17 @@ static int files_roundtrip(const std::vector<uint8_t>& data, const avr::FileReco
   if (!ds.empty())
     avr_decompress_file_host(fd, ds.data(), pool.data(), est.data(), s0.data(), s1.data(), row.data(), &tab, out.data(), olen.data(),
                              obins.data(), status.data());
+  if (fuzz_flips) {
+    int nerr = 0; for (int v : status) nerr += v != 0;
+    if (nerr) { printf("TERMINATED slices=%zu with_status=%d\n", ds.size(), nerr); return 0; }
+  }
   for (size_t k = 0; k < ds.size(); k++) if (status[k]) { printf("slice %zu: status %d\n", k, status[k]); return 1; }
   uint8_t* back = nullptr; size_t back_n = 0;
   if (!avrc::assemble(d, [&](uint32_t k, const uint8_t** p, uint32_t* len) { *p = out.data() + ds[k].out_off; *len = olen[k]; }, &back, &back_n)) return 2;
   const bool same = back_n == data.size() && memcmp(back, data.data(), back_n) == 0;
   free(back);
   size_t nskip = 0; for (auto& b : d.blocks) nskip += b.has_skip;
+  if (fuzz_flips) { printf("TERMINATED restored=%d\n", (int)same); return 0; }
   printf("%s container=%zu bytes of %zu, blocks=%zu coded=%zu skip_coded=%zu\n", same ? "OK" : "FAIL", cont.n, data.size(), d.blocks.size(), ds.size(), nskip);
   return same ? 0 : 1;
 }
@@ -393,6 +413,7 @@ int main(int argc, char** argv) {
     c = all.back();
   }
   if (cmd == "files") return files_roundtrip(data, rec, tab, argc > 3 ? argv[3] : nullptr);
+  if (cmd == "filesfuzz") return files_roundtrip(data, rec, tab, nullptr, fseed, fflips);
   if (cmd == "parse") return parse_check(data, rec, tab);
   if (cmd == "roundtrip") return decompress_check(data, rec, tab, c) ? 1 : 0;
   for (auto& p : c.payloads) print_hex("P ", p.data(), p.size());

@@ -286,3 +286,13 @@ def test_random_bit_flips_round_trip(tmp_path):
         clip.write_bytes(bytes(d))
         rc, out, err = run([EMUL, "files", str(clip)])
         assert rc == 0 and out.startswith(b"OK"), (name, i, out, err)
+
+
+@pytest.mark.parametrize("name", GOLDEN_NAMES)
+def test_corrupted_container_ends_with_a_status_inside_its_buffers(name):
+    """bit flips in the .avrec itself (what avr_decompress_files receives from outside): container reader, surrogate scan, plan and
+    the decompress body under ASan/UBSan must end with a status or a wrong file, never outside their buffers
+    (420 cases by hand: none)"""
+    for seed in range(1, 9):
+        rc, out, err = run([EMUL_ASAN, "filesfuzz", os.path.join(GOLDEN, name + ".h264"), str(seed), str(1 + seed % 6)])
+        assert rc == 0 and out.startswith(b"TERMINATED"), (seed, out, err[-400:])
