@@ -777,6 +777,13 @@ extern "C" int avr_cbatch_create_files(avr_context* ctx, const uint8_t* const* f
   b->t.h2d_ms = ev_ms(ctx->ev[0], ctx->ev[1]); b->t.parse_ms = ev_ms(ctx->ev[1], ctx->ev[2]); b->t.launches = 1;
   // files with a failed slice drop out of the batch
   for (uint32_t s = 0; s < ns; s++) if (res[s].status && !file_status[ps_file[s]]) file_status[ps_file[s]] = res[s].status;
+  // Slices of one picture must not overlap (a damaged slice can run past the next one's first macroblock and still end cleanly):
+  // the slice-parallel passes need every macroblock position coded at most once per picture store.  Such a file goes to the host
+  // recorder, which stores it literally (avr_record.cpp record_annexb).
+  for (uint32_t s = 1; s < ns; s++)
+    if (ps_file[s] == ps_file[s - 1] && ps[s].frame == ps[s - 1].frame && !file_status[ps_file[s]] &&
+        (uint64_t)ps[s - 1].sp.first_mb + res[s - 1].mbs > (uint64_t)ps[s].sp.first_mb)
+      file_status[ps_file[s]] = AVR_E_CORRUPT;
   // dense layout of what remains
   std::vector<AvrFileDesc> fds((size_t)nfiles);
   std::vector<AvrBatchSlice> bsl; std::vector<AvrFrame> frames;

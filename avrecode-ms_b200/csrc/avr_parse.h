@@ -30,6 +30,7 @@ struct AvrParseSlice {
 struct AvrParseResult {
   uint32_t nbins, nblocks, emitted;
   int status;
+  uint32_t mbs;            // macroblocks the slice covers (the host checks that slices of one picture do not overlap)
 };
 
 // before the parse: the bytes that follow a payload in the pool become the bytes libavcodec's buffer holds there
@@ -360,7 +361,7 @@ AVR_PAR_FN void avr_parse_slice(const AvrParseSlice& ps, const uint8_t* raw, uin
   // ... and through end_of_slice_flag = 1, not by running out of macroblocks: the decompress chain could not close such a slice
   if (rc >= 0 && g_par.nb >= 1 && g_par.nb <= g_par.bin_cap && g_par.bins[g_par.nb - 1] != AVR_BIN(1, AVR_CTX_TERMINATE, AVR_KIND_DEFAULT))
     rc = avr::SYN_E_LENGTH;
-  res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted;
+  res->nbins = g_par.nb; res->nblocks = g_par.nblk; res->emitted = g_par.emitted; res->mbs = rc > 0 ? (uint32_t)rc : 0u;
   const int over = g_par.nb > g_par.bin_cap || g_par.nblk > g_par.blk_cap;
   res->status = over ? AVR_E_OVERFLOW : rc == avr::SYN_E_PCM ? AVR_E_UNSUPPORTED : rc < 0 ? AVR_E_CORRUPT : AVR_OK;
 }

@@ -118,7 +118,7 @@ int scan_annexb(const uint8_t* data, size_t n, FileRecord* out, std::vector<Scan
 int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
   Recorder rec(out, trace);
   std::vector<MbInfo> row;
-  uint32_t uid = 0;
+  uint32_t uid = 0, cover_frame = ~0u, cover_end = 0;
   size_t prev_coded_end = 0;
   int rc = scan_annexb_slices(data, n, [&](const SliceLoc& loc) -> int {
     const SliceHeaderInfo& sh = loc.sh;
@@ -150,6 +150,11 @@ int record_annexb(const uint8_t* data, size_t n, FileRecord* out, FILE* trace) {
       return 0;
     }
     rec.slice_end();
+    // Slices of one picture must not overlap: a damaged slice can run past the next one's first macroblock and still end cleanly, and
+    // the slice-parallel compress passes need every macroblock position coded at most once per picture store.  The damaged one is
+    // already recorded by then: the whole file is stored literally (the caller's fallback for a non-zero result).
+    if (rec.cur_frame() == cover_frame && (uint32_t)sh.sp.first_mb < cover_end) return AVR_E_UNSUPPORTED;
+    cover_frame = rec.cur_frame(); cover_end = (uint32_t)sh.sp.first_mb + (uint32_t)prc;
     return 0;
   }, &out->skipped_slices);
   out->error = rc;

@@ -387,6 +387,17 @@ int main(int argc, char** argv) {
   }
   avr::FileRecord rec;
   int rc = avr::record_annexb(data.data(), data.size(), &rec);
+  if (rc && cmd == "files") {
+    // what avr_compress_files does with a file the recorder refuses as a whole: one literal block (avr_files.cpp)
+    avrc::Buf cont; avrc::put_block_literal(cont, data.data(), data.size());
+    avrc::DFile d; avrc::plan_decompress(cont.p, cont.n, &d);
+    uint8_t* back = nullptr; size_t back_n = 0;
+    const bool ok = !d.rc && avrc::assemble(d, [](uint32_t, const uint8_t**, uint32_t*) {}, &back, &back_n) && back_n == data.size() &&
+                    memcmp(back, data.data(), back_n) == 0;
+    free(back);
+    printf("%s container=%zu bytes of %zu, blocks=1 coded=0 skip_coded=0 (record rc=%d: whole file literal)\n", ok ? "OK" : "FAIL", cont.n, data.size(), rc);
+    return ok ? 0 : 1;
+  }
   if (rc) { fprintf(stderr, "record rc=%d\n", rc); return 1; }
   AvrTables tab;
   avr_fill_tables(&tab);

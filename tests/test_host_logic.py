@@ -296,3 +296,20 @@ def test_corrupted_container_ends_with_a_status_inside_its_buffers(name):
     for seed in range(1, 9):
         rc, out, err = run([EMUL_ASAN, "filesfuzz", os.path.join(GOLDEN, name + ".h264"), str(seed), str(1 + seed % 6)])
         assert rc == 0 and out.startswith(b"TERMINATED"), (seed, out, err[-400:])
+
+
+def test_slices_of_one_picture_must_not_overlap(tmp_path):
+    """found by tools/cpu_bitflip_sweep.py (1 of 2000 four-flip cases): two flips inside the first slice of a picture of skippy_idr.h264 leave
+    it ending cleanly (right bit, end_of_slice_flag = 1) but running past the next slice's first macroblock; positions coded twice in
+    one picture store break the slice-parallel compress passes (chain != pipeline).  The recorder refuses the file (stored literally),
+    the file API's device path flags it from the parse results (avr_api.cu)"""
+    d = bytearray(open(os.path.join(GOLDEN, "skippy_idr.h264"), "rb").read())
+    d[3447] ^= 1 << 6
+    d[3270] ^= 1 << 3
+    clip = tmp_path / "overlap.h264"
+    clip.write_bytes(bytes(d))
+    tool = os.path.join(ROOT, "avrecode-ms_b200", "bin", "avrtool")
+    rc, _, err = run([tool, "stats", str(clip)])
+    assert rc != 0 and b"rc=-4" in err, err
+    rc, out, err = run([EMUL_ASAN, "files", str(clip)])
+    assert rc == 0 and out.startswith(b"OK") and b"whole file literal" in out, out + err
